@@ -543,3 +543,41 @@ void or_extract_forces_flat(const OrEnv* e, double* out) {
   memcpy(out, &F, sizeof(F));
 }
 int or_forces_size(void) { return (int)(sizeof(OrForces) / sizeof(double)); }
+
+/* flat state view for parity checks (mirrors OrPeek in oracle/binding.py) */
+typedef struct {
+  double qpos[96], qvel[96], time, wrist_z;
+  int ncon, nrow, niter, unstable;
+  double tgt_end[4], tgt_next[4];
+  int tgt_steps[6];
+  double base_z;
+  int weld_on[7], pad;
+  double reset_qpos[8];
+  float si[5], pad2;
+  double con_dist[24], con_force[72], con_pos[72], con_normal[72];
+  int con_cls[48];
+  int64_t substeps, contacts, rows, iters;
+} OrPeek;
+
+void or_peek(const OrEnv* e, OrPeek* p) {
+  memset(p, 0, sizeof(*p));
+  for (int i = 0; i < e->nq && i < 96; i++) p->qpos[i] = e->qpos[i];
+  for (int i = 0; i < e->nv && i < 96; i++) p->qvel[i] = e->qvel[i];
+  p->time = e->time; p->wrist_z = e->wrist_z;
+  p->ncon = e->ncon; p->nrow = e->nrow; p->niter = e->niter; p->unstable = e->unstable;
+  p->tgt_end[0] = e->tgt_end.x; p->tgt_end[1] = e->tgt_end.y; p->tgt_end[2] = e->tgt_end.z; p->tgt_end[3] = e->tgt_end.th;
+  p->tgt_next[0] = e->tgt_next.x; p->tgt_next[1] = e->tgt_next.y; p->tgt_next[2] = e->tgt_next.z; p->tgt_next[3] = e->tgt_next.th;
+  p->tgt_steps[0] = e->tgt_end.sx; p->tgt_steps[1] = e->tgt_end.sy; p->tgt_steps[2] = e->tgt_end.sz;
+  p->tgt_steps[3] = e->tgt_next.sx; p->tgt_steps[4] = e->tgt_next.sy; p->tgt_steps[5] = e->tgt_next.sz;
+  p->base_z = e->base_z;
+  for (int i = 0; i < 7; i++) p->weld_on[i] = e->weld[i].on;
+  for (int i = 0; i < 8; i++) p->reset_qpos[i] = e->reset_qpos[i];
+  for (int k = 0; k < 3; k++) p->si[k] = or_win_read(&e->si_gauge[k], 0);
+  p->si[3] = or_win_read(&e->si_palm, 0); p->si[4] = or_win_read(&e->si_wristz, 0);
+  for (int c = 0; c < e->ncon; c++) {
+    p->con_dist[c] = e->con[c].dist;
+    for (int k = 0; k < 3; k++) { p->con_force[3 * c + k] = e->con[c].force[k]; p->con_pos[3 * c + k] = e->con[c].pos[k]; p->con_normal[3 * c + k] = e->con[c].frame[k]; }
+    p->con_cls[2 * c] = e->con[c].cls1; p->con_cls[2 * c + 1] = e->con[c].cls2;
+  }
+  p->substeps = e->st_substeps; p->contacts = e->st_contacts; p->rows = e->st_rows; p->iters = e->st_iters;
+}

@@ -320,10 +320,14 @@ void or_physics_step(OrEnv* e) {
       Rr[r] = fmax(1e-15, (1 - imp) / imp * A[r][r]);
       bvec[r] = ja - aref[r];
     }
-    /* pyramidal contacts: all edges share R = 2 mu^2 R(first edge) */
+    /* pyramidal contacts (mj_makeImpedance): every edge of a contact shares
+     * R = 2 mu^2 (1-d)/d diagApprox, diagApprox = (1 + mu^2) * A_nn, where A_nn is the diagonal of
+     * the pure normal direction n = (e0 + e1)/2 (MuJoCo approximates it by body inverse weights) */
     for (int c = 0; c < e->ncon; c++) {
       int r0 = e->con[c].row; double mu = e->con[c].mu;
-      double Rpy = 2 * mu * mu * Rr[r0];
+      double imp = impedance(m->solimp, rpos[r0]);
+      double Ann = 0.25 * (A[r0][r0] + A[r0 + 1][r0 + 1] + 2 * A[r0][r0 + 1]);
+      double Rpy = 2 * mu * mu * (1 - imp) / imp * (1 + mu * mu) * Ann;
       for (int k = 0; k < 4; k++) Rr[r0 + k] = fmax(1e-15, Rpy);
     }
   }

@@ -270,7 +270,7 @@ void or_physics_step(OrEnv* e) {
         double v = (d < 3) ? (Jp2[d * nv + j] - Jp1[d * nv + j]) : (Jr2[(d - 3) * nv + j] - Jr1[(d - 3) * nv + j]);
         J[nr][j] = v; nz += v * v;
       }
-      if (nz < 1e-20) continue;
+      if (nz < 1e-10) continue;   /* |J| < 1e-5: structurally zero row */
       rpos[nr] = (d < 3) ? r[d] : rr[d - 3];
       rtype[nr] = ROW_EQ;
       nr++;

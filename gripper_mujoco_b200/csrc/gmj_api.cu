@@ -1,0 +1,399 @@
+// gmj_api.cu -- kernels + C ABI (include/gmj.h) of libgripper_b200.so.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/gmj.h"
+#include "gmj_physics.cuh"
+
+#define WARPS_PER_BLOCK 4
+
+static thread_local std::string g_err;
+#define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) { g_err = std::string(#x) + ": " + cudaGetErrorString(_e); return 1; } } while (0)
+#define FAIL(msg) do { g_err = (msg); return 1; } while (0)
+
+// ------------------------------------------------------------------------------------------ kernels
+enum { STEP_SET_ACTION = 1, STEP_SUBSTEPS = 2, STEP_TAIL = 4, STEP_OUTPUT = 8, STEP_SENSORS = 16 };
+
+template <typename T> __device__ __forceinline__ void copy_words(void* dst, const void* src, int nbytes, int lane) {
+  const uint32_t* s = (const uint32_t*)src; uint32_t* d = (uint32_t*)dst;
+  for (int i = lane; i < nbytes / 4; i += 32) d[i] = s[i];
+}
+
+// One warp per environment. flags select the phases so the same kernel serves gmj_step (all),
+// gmj_set_action, gmj_action_step, gmj_substeps and gmj_observe.
+template <typename T, int N>
+__global__ void __launch_bounds__(32 * WARPS_PER_BLOCK)
+k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const DevSettings* __restrict__ Sp, int n_envs,
+       int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
+       float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,
+       int* __restrict__ err_flag) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int env = blockIdx.x * WARPS_PER_BLOCK + warp;
+  if (env >= n_envs) return;
+  WarpShared<T, N>& ws = *reinterpret_cast<WarpShared<T, N>*>(smem_raw + (size_t)warp * sizeof(WarpShared<T, N>));
+  const DevModel<T>& M = *Mp; const DevSettings& S = *Sp;
+  copy_words<T>(&ws.e, &envs[env], sizeof(EnvState<T>), lane);
+  if (lane == 0) { ws.ax.ncon = 0; ws.ax.nrow = 0; ws.ax.niter = 0; ws.ax.wrist_z = ws.e.wrist_z; }
+  ws.qfk[lane] = ws.e.qpos[lane];
+  __syncwarp();
+  EnvState<T>& e = ws.e;
+  int extra = 0;
+  if (flags & STEP_SET_ACTION) {
+    if (lane == 0) {
+      extra = set_action<T>(e, S, M, actions[env], frac ? frac[env] : 0.0f);
+      if (extra < 0) { extra = 0; if (err_flag) atomicExch(err_flag, 1); }
+    }
+    extra = __shfl_sync(GMJ_FULL, extra, 0);
+    __syncwarp();
+  }
+  if (flags & STEP_SUBSTEPS) {
+    const int nsub = extra + (nsub_override >= 0 ? nsub_override : (int)S.s.general[GS_sim_steps_per_action]);
+    const double dtd = S.s.general[GS_mujoco_timestep];
+    const bool curve = S.s.general[GS_curve_validation] != 0;
+    const T tipf = curve ? (T)S.s.general[GS_tip_force_applied] : T(0);
+    for (int i = 0; i < nsub; i++) {
+      if (curve && lane == 0) for (int id = 0; id < 6; id++) set_weld<T, N>(e, id, 1, ws.qfk);   // apply_segment_force re-locks every step
+      __syncwarp();
+      physics_substep<T, N>(ws, M, S, lane, dtd, tipf);
+      if (lane == 0) {
+        update_all<T, N>(e, ws.qfk);
+        if (flags & STEP_SENSORS) monitor_sensors<T, N>(e, S, M, ws.ax);
+      }
+      __syncwarp();
+    }
+    if (lane == 0) e.wrist_z = (float)ws.ax.wrist_z;
+  }
+  if ((flags & STEP_TAIL) && lane == 0) {
+    sense_gripper_state<T>(e, S, M);
+    update_env<T>(e, S, ws.ax);
+    e.num_action_steps += 1;
+  }
+  if ((flags & STEP_OUTPUT) && lane == 0) {
+    if (reward) { float r = calc_reward<T>(e, S); e.last_reward = r; reward[env] = r; }
+    int d = calc_done<T>(e, S); e.last_done = d;
+    if (done) done[env] = (uint8_t)d;
+    if (obs) get_observation<T>(e, S, obs + (size_t)env * S.n_obs);
+    if (events) event_state<T>(e, events + (size_t)env * GMJ_EVENT_STATE_LEN);
+  }
+  __syncwarp();
+  copy_words<T>(&envs[env], &ws.e, sizeof(EnvState<T>), lane);
+}
+
+// MjClass::reset + luke::reset (src/mjclass.cpp:434-486, src/myfunctions.cpp:544-570): one thread per env
+template <typename T>
+__global__ void k_reset(EnvState<T>* envs, const DevModel<T>* Mp, const DevSettings* Sp, int n_envs,
+                        const uint8_t* mask, uint32_t env_id_offset) {
+  int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= n_envs) return;
+  if (mask && !mask[env]) return;
+  EnvState<T>& e = envs[env];
+  const DevModel<T>& M = *Mp; const DevSettings& S = *Sp;
+  const int N = M.N, NL = N + 2, B = M.B;
+  uint32_t episode = e.episode + 1;
+  unsigned long long c0 = e.st_contacts, c1 = e.st_rows, c2 = e.st_iters, c3 = e.st_substeps; unsigned int c4 = e.st_unstable + (e.unstable ? 1 : 0), c5 = e.st_overflow;
+  memset(&e, 0, sizeof(EnvState<T>));
+  e.st_contacts = c0; e.st_rows = c1; e.st_iters = c2; e.st_substeps = c3; e.st_unstable = c4; e.st_overflow = c5;
+  e.episode = episode; e.env_id = env_id_offset + env; e.rng_ctr = episode << 12;
+  g_reset(e.tend); g_reset(e.tnext);
+  for (int i = 0; i < B; i++) e.qpos[i] = M.f[MF_qpos0][i];
+  // parked object (dead collision group): not simulated
+  e.qpos[32] = 0; e.qpos[33] = 2; e.qpos[34] = 1; e.qpos[35] = 0; e.qpos[36] = 0; e.qpos[37] = 0; e.qpos[38] = 1;
+  // weld anchors from the keyframe pose (xpos/xmat are stale when set_all_constraints runs), then
+  // the stored equilibrium of base + motor joints (calibrate_reset)
+  for (int f = 0; f < 3; f++) { e.weld_anchor[f] = e.qpos[1 + f * NL]; e.weld_anchor[3 + f] = e.qpos[2 + f * NL]; }
+  e.weld_anchor[6] = e.qpos[B - 1];
+  e.weld_on = 0x7f; e.old_moving = 0;
+  const double* g = S.s.general;
+  e.qpos[0] = (T)g[GS_reset_qpos_base];
+  for (int f = 0; f < 3; f++) { e.qpos[1 + f * NL] = (T)g[GS_reset_qpos_g0 + 2 * f]; e.qpos[2 + f * NL] = (T)g[GS_reset_qpos_g1 + 2 * f]; }
+  e.qpos[B - 1] = (T)g[GS_reset_qpos_g6];
+  for (int s = 0; s < GMJ_NSTREAM; s++) e.win_i[s] = -1;
+  // Settings::apply_noise_params (src/mjclass.cpp:5293-5346)
+  for (int k = 0; k < GSEN_COUNT; k++) {
+    float mu = (float)(S.s.sensor[k][GSF_noise_overriden] ? S.s.sensor[k][GSF_noise_mu] : g[GS_sensor_noise_mu]);
+    for (int j = 0; j < 3; j++) e.rand_mu[k][j] = mu * (2 * dev_uniform(e, S) - 1);
+  }
+  const int state_sensors[5] = { GSEN_motor_state, GSEN_base_XY, GSEN_base_Z, GSEN_base_yaw, GSEN_cartesian };
+  for (int qn = 0; qn < 5; qn++) {
+    int k = state_sensors[qn];
+    float mu = (float)(S.s.sensor[k][GSF_noise_overriden] ? S.s.sensor[k][GSF_noise_mu] : g[GS_state_noise_mu]);
+    for (int j = 0; j < 3; j++) e.rand_mu[k][j] = mu * (2 * dev_uniform(e, S) - 1);
+  }
+  // random_base_Z_movement (src/mjclass.cpp:1423-1434)
+  double size = g[GS_base_position_noise];
+  double zmove = (g[GS_use_noise_seeded] && size > 0) ? (-size + 2 * size * (double)dev_uniform(e, S)) : 0.0;
+  float zf = (float)zmove;
+  e.base_z = zf;
+  if (e.base_z > g[GS_base_z_max]) e.base_z = g[GS_base_z_max];
+  if (e.base_z < g[GS_base_z_min]) e.base_z = g[GS_base_z_min];
+  e.qpos[0] = (T)(e.base_z + g[GS_reset_qpos_base]);
+}
+
+// luke::Box2d::overlapsWith (src/customtypes.h:86-140)
+__device__ inline void box2d_init(double* b, double cx, double cy, double w, double h, double theta) {
+  double hw = w / 2.0, hh = h / 2.0;
+  b[0] = cx - hw; b[4] = cy - hh; b[1] = cx + hw; b[5] = cy - hh; b[2] = cx + hw; b[6] = cy + hh; b[3] = cx - hw; b[7] = cy + hh;
+  double mx = (b[0] + b[1] + b[2] + b[3]) / 4.0, my = (b[4] + b[5] + b[6] + b[7]) / 4.0;
+  for (int i = 0; i < 4; i++) {
+    double nx = mx + (b[i] - mx) * cos(theta) - (b[4 + i] - my) * sin(theta);
+    double ny = my + (b[i] - mx) * sin(theta) + (b[4 + i] - my) * cos(theta);
+    b[i] = nx; b[4 + i] = ny;
+  }
+}
+__device__ inline int box2d_overlap(const double* a, const double* o, double min_distance) {
+  int contains_other = 1;
+  for (int i = 0; i < 4; i++) {
+    int j = (i + 1) % 4;
+    double ex = a[j] - a[i], ey = a[4 + j] - a[4 + i];
+    double px = -ey, py = ex, len = sqrt(px * px + py * py);
+    px /= len; py /= len;
+    double min1 = a[0] * px + a[4] * py, max1 = min1, min2 = o[0] * px + o[4] * py, max2 = min2;
+    for (int k = 1; k < 4; k++) {
+      double p1 = a[k] * px + a[4 + k] * py, p2 = o[k] * px + o[4 + k] * py;
+      if (p1 < min1) min1 = p1; if (p1 > max1) max1 = p1; if (p2 < min2) min2 = p2; if (p2 > max2) max2 = p2;
+    }
+    if (max1 + min_distance < min2 || max2 + min_distance < min1) return 0;
+    if (max1 < min2 || max2 < min1) contains_other = 0;
+  }
+  return contains_other;
+}
+
+// MjClass::spawn_object / spawn_into_scene (src/mjclass.cpp:2352-2420,2475-2654)
+template <typename T>
+__global__ void k_spawn(EnvState<T>* envs, const DevModel<T>* Mp, const DevSettings* Sp, const GmjObject* objects, int n_objects,
+                        int n_envs, const int32_t* idx, const float* xyr, const uint8_t* mask, float xy_range, float rot_range,
+                        int* err_flag) {
+  int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= n_envs) return;
+  if (mask && !mask[env]) return;
+  EnvState<T>& e = envs[env];
+  const DevSettings& S = *Sp; const DevModel<T>& M = *Mp;
+  int oi; double x, y, rot;
+  if (idx) {
+    oi = idx[env]; x = xyr[3 * env]; y = xyr[3 * env + 1]; rot = xyr[3 * env + 2];
+    if (oi < 0 || oi >= n_objects) { if (err_flag) atomicExch(err_flag, 2); return; }
+  } else {
+    // object index and pose from the counter-based RNG; candidate grid as in spawn_into_scene
+    // (2 mm steps within +-xy_range, pi/30 steps within +-rot_range), fingertip boxes from
+    // luke::get_finger_hook_locations (src/myfunctions.cpp:3717-3761), up to 16 candidates
+    oi = (int)(dev_uniform(e, S) * n_objects); if (oi >= n_objects) oi = n_objects - 1;
+    const GmjObject& ob = objects[oi];
+    const double inc = 2e-3, rinc = 3.14159265358979323846 / 30.0, gap = 1e-3;
+    int nx = (int)((2 * (double)xy_range) / inc) + 1, nrot = (int)((2 * (double)rot_range) / rinc) + 1;
+    double tips[3][8];
+    const double hook_th = (double)M.hook_angle_deg * (3.14159265358979323846 / 180.000);
+    const double hookx = 0.5 * (double)M.hook_length * sin(hook_th);
+    for (int i = 0; i < 3; i++) {
+      double ang = i * (3.14159265358979323846 * (2.0 / 3.0));
+      double px = -(e.tend.x - hookx) * sin(ang) + e.base_x, py = -(e.tend.x - hookx) * cos(ang) + e.base_y;
+      box2d_init(tips[i], px, py, (double)M.finger_width, (double)M.hook_length, -ang);
+    }
+    x = 0; y = 0; rot = 0;
+    for (int t = 0; t < 16; t++) {
+      int ix = (int)(dev_uniform(e, S) * nx), iy = (int)(dev_uniform(e, S) * nx), ir = (int)(dev_uniform(e, S) * nrot);
+      if (ix >= nx) ix = nx - 1; if (iy >= nx) iy = nx - 1; if (ir >= nrot) ir = nrot - 1;
+      x = nx > 1 ? -(double)xy_range + ix * inc : 0.0; y = nx > 1 ? -(double)xy_range + iy * inc : 0.0;
+      rot = nrot > 1 ? -(double)rot_range + ir * rinc : 0.0;
+      double ours[8];
+      box2d_init(ours, x, y, ob.bbox[0], ob.bbox[1], rot);
+      int ok = 1;
+      for (int i = 0; i < 3 && ok; i++) if (box2d_overlap(ours, tips[i], gap)) ok = 0;
+      if (ok) break;
+    }
+  }
+  const GmjObject& ob = objects[oi];
+  e.obj[0] = (T)ob.type; e.obj[1] = (T)ob.size[0]; e.obj[2] = (T)ob.size[1]; e.obj[3] = (T)ob.size[2]; e.obj[4] = (T)ob.round;
+  e.obj[5] = (T)ob.quat[0]; e.obj[6] = (T)ob.quat[1]; e.obj[7] = (T)ob.quat[2]; e.obj[8] = (T)ob.quat[3];
+  e.obj[9] = (T)ob.mass; e.obj[10] = (T)ob.inertia[0]; e.obj[11] = (T)ob.inertia[1]; e.obj[12] = (T)ob.inertia[2];
+  e.obj[13] = (T)ob.friction; e.obj[14] = (T)ob.z_rest;
+  e.obj_index = oi; e.has_object = 1;
+  double z = ob.z_rest + 1e-6;
+  e.qpos[32] = (T)x; e.qpos[33] = (T)y; e.qpos[34] = (T)z;
+  e.qpos[35] = (T)sin(-rot / 2.0); e.qpos[36] = 0; e.qpos[37] = 0; e.qpos[38] = (T)cos(-rot / 2.0);
+  for (int k = 0; k < 6; k++) e.qvel[32 + k] = 0;
+  e.start_z = (double)(T)z;
+  e.nrow_prev = 0;
+}
+
+template <typename T>
+__global__ void k_dump(const EnvState<T>* envs, int n_envs, int B, double* qpos, double* qvel, double* probe) {
+  int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= n_envs) return;
+  const EnvState<T>& e = envs[env];
+  if (qpos) { for (int i = 0; i < B; i++) qpos[(size_t)env * (B + 7) + i] = (double)e.qpos[i]; for (int k = 0; k < 7; k++) qpos[(size_t)env * (B + 7) + B + k] = (double)e.qpos[32 + k]; }
+  if (qvel) { for (int i = 0; i < B; i++) qvel[(size_t)env * (B + 6) + i] = (double)e.qvel[i]; for (int k = 0; k < 6; k++) qvel[(size_t)env * (B + 6) + B + k] = (double)e.qvel[32 + k]; }
+  if (probe) {
+    double* p = probe + (size_t)env * GMJ_PROBE_LEN;
+    for (int k = 0; k < GMJ_PROBE_LEN; k++) p[k] = 0;
+    p[GP_time] = e.time; p[GP_wrist_z] = e.wrist_z;
+    for (int k = 0; k < 5; k++) p[GP_si_gauge0 + k] = e.si_latest[k];
+    p[GP_unstable] = e.unstable; p[GP_weld_on] = e.weld_on; p[GP_base_z] = e.base_z;
+    p[GP_tend_x] = e.tend.x; p[GP_tend_y] = e.tend.y; p[GP_tend_z] = e.tend.z; p[GP_tend_th] = e.tend.th;
+    p[GP_tnext_x] = e.tnext.x; p[GP_tnext_y] = e.tnext.y; p[GP_tnext_z] = e.tnext.z; p[GP_tnext_th] = e.tnext.th;
+    p[GP_cumulative_reward] = e.cumulative_reward; p[GP_has_object] = e.has_object; p[GP_obj_index] = e.obj_index;
+    p[GP_episode] = e.episode; p[GP_last_reward] = e.last_reward; p[GP_last_done] = e.last_done;
+    p[GP_nrow] = e.nrow_prev;
+  }
+}
+
+template <typename T, int N>
+__global__ void k_gauge(const EnvState<T>* envs, const DevModel<T>* Mp, int n_envs, double* probe) {
+  int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= n_envs) return;
+  for (int f = 0; f < 3; f++) probe[(size_t)env * GMJ_PROBE_LEN + GP_gauge0 + f] = (double)read_gauge<T, N>(envs[env], *Mp, f);
+}
+
+template <typename T>
+__global__ void k_set_welds(EnvState<T>* envs, int n_envs, int B, int N, int mask_on) {
+  int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= n_envs) return;
+  EnvState<T>& e = envs[env];
+  for (int id = 0; id < 7; id++) {
+    if ((mask_on >> id) & 1) {
+      int j = (id < 3) ? (1 + id * (N + 2)) : ((id < 6) ? (2 + (id - 3) * (N + 2)) : (B - 1));
+      e.weld_anchor[id] = e.qpos[j];
+    }
+  }
+  e.weld_on = mask_on & 0x7f;
+}
+
+template <typename T>
+__global__ void k_stats(const EnvState<T>* envs, int n_envs, unsigned long long* out) {
+  int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= n_envs) return;
+  const EnvState<T>& e = envs[env];
+  atomicAdd(&out[0], e.st_substeps); atomicAdd(&out[1], (unsigned long long)(e.st_unstable + (e.unstable ? 1 : 0)));
+  atomicAdd(&out[2], e.st_contacts); atomicAdd(&out[3], e.st_rows); atomicAdd(&out[4], e.st_iters);
+  atomicAdd(&out[5], (unsigned long long)e.st_overflow);
+}
+
+// ------------------------------------------------------------------------------------------ host side
+struct GmjHandle {
+  int n_envs, device, precision, N, B;
+  uint32_t env_id_offset;
+  void* envs;            // EnvState<T>[n_envs]
+  void* model;           // DevModel<T>
+  DevSettings* settings; // device
+  DevSettings hs;        // host copy
+  GmjObject* objects; int n_objects;
+  int* err_flag;
+  unsigned long long* stats_dev;
+  double* scratch; size_t scratch_len;
+  GmjModel hm;
+  size_t smem_bytes;
+};
+
+static void quat2mat_h(const double* q, double* R) {
+  double w = q[0], x = q[1], y = q[2], z = q[3];
+  R[0] = 1 - 2 * (y * y + z * z); R[1] = 2 * (x * y - w * z); R[2] = 2 * (x * z + w * y);
+  R[3] = 2 * (x * y + w * z); R[4] = 1 - 2 * (x * x + z * z); R[5] = 2 * (y * z - w * x);
+  R[6] = 2 * (x * z - w * y); R[7] = 2 * (y * z + w * x); R[8] = 1 - 2 * (x * x + y * y);
+}
+
+template <typename T>
+static int build_model(const GmjModel* m, DevModel<T>* d) {
+  memset(d, 0, sizeof(*d));
+  const int N = m->N, NL = N + 2, B = m->B;
+  if (m->nb != 1) FAIL("only nb = 1 (world_to_base) is supported");
+  if (B != 3 * N + 8 || B > 32) FAIL("lane-per-dof layout needs B = 3N + 8 <= 32 (N <= 8)");
+  d->N = N; d->B = B; d->NL = NL; d->palm_lane = B - 1;
+  d->zref = (T)0.2;
+  for (int i = 0; i < 32; i++) { d->f[MF_gtype][i] = -1; d->f[MF_htype][i] = -1; d->f[MF_mass][i] = 0; d->f[MF_R0][i] = d->f[MF_R4][i] = d->f[MF_R8][i] = 1; }
+  for (int i = 0; i < B; i++) {
+    double R[9]; quat2mat_h(m->quat[i], R);
+    d->f[MF_parent][i] = (T)m->parent[i]; d->f[MF_jtype][i] = (T)m->jtype[i]; d->f[MF_group][i] = (T)m->group[i];
+    for (int k = 0; k < 3; k++) { d->f[MF_pos0 + k][i] = (T)m->pos[i][k]; d->f[MF_ax0 + k][i] = (T)m->axis[i][k]; d->f[MF_ip0 + k][i] = (T)m->ipos[i][k]; }
+    if (m->parent[i] < 0) d->f[MF_pos2][i] = (T)(m->pos[i][2] - (double)d->zref);
+    for (int k = 0; k < 9; k++) d->f[MF_R0 + k][i] = (T)R[k];
+    d->f[MF_mass][i] = (T)m->mass[i];
+    for (int k = 0; k < 6; k++) d->f[MF_ixx + k][i] = (T)m->inertia[i][k];
+    d->f[MF_stiff][i] = (T)m->stiffness[i]; d->f[MF_damp][i] = (T)m->damping[i];
+    d->f[MF_lo][i] = (T)m->range_lo[i]; d->f[MF_hi][i] = (T)m->range_hi[i]; d->f[MF_qpos0][i] = (T)m->qpos0[i];
+    // structural checks for the lane layout
+    int exp_parent = (i == 0) ? -1 : ((i == B - 1) ? 0 : (((i - 1) % NL == 0) ? 0 : i - 1));
+    if (m->parent[i] != exp_parent) FAIL("model tree does not match the lane layout");
+    int exp_hinge = (i != 0 && i != B - 1 && ((i - 1) % NL) > 0);
+    if (m->jtype[i] != exp_hinge) FAIL("model joint types do not match the lane layout");
+  }
+  // PD control (src/myfunctions.cpp:1965-2057): target selector 1 base z, 2 x, 3 th, 4 z
+  d->f[MF_tsel][0] = 1; d->f[MF_kp][0] = (T)m->base_kp; d->f[MF_kd][0] = (T)m->base_kd;
+  for (int f = 0; f < 3; f++) {
+    int ip = 1 + f * NL;
+    d->f[MF_tsel][ip] = 2; d->f[MF_kp][ip] = (T)m->kp[0]; d->f[MF_kd][ip] = (T)m->kd[0];
+    d->f[MF_tsel][ip + 1] = 3; d->f[MF_kp][ip + 1] = (T)m->kp[1]; d->f[MF_kd][ip + 1] = (T)m->kd[1];
+  }
+  d->f[MF_tsel][B - 1] = 4; d->f[MF_kp][B - 1] = (T)m->kp[2]; d->f[MF_kd][B - 1] = (T)m->kd[2];
+  // geoms: first geom of a body is its primary, a second one (the hook plate) goes to the h* slot
+  for (int g = 0; g < m->ngeom; g++) {
+    int b = m->g_body[g];
+    double R[9]; quat2mat_h(m->g_quat[g], R);
+    int base = (d->f[MF_gtype][b] < 0) ? MF_gtype : ((d->f[MF_htype][b] < 0) ? MF_htype : -1);
+    if (base < 0) FAIL("more than two collision geoms on one body");
+    if (base == MF_gtype) {
+      d->f[MF_gtype][b] = (T)m->g_type[g]; d->f[MF_gfric][b] = (T)m->g_friction[g]; d->f[MF_gcls][b] = (T)m->g_class[g];
+      for (int k = 0; k < 3; k++) { d->f[MF_gp0 + k][b] = (T)m->g_pos[g][k]; d->f[MF_gs0 + k][b] = (T)m->g_size[g][k]; }
+      for (int k = 0; k < 9; k++) d->f[MF_gR0 + k][b] = (T)R[k];
+    } else {
+      d->f[MF_htype][b] = (T)m->g_type[g];
+      for (int k = 0; k < 3; k++) { d->f[MF_hp0 + k][b] = (T)m->g_pos[g][k]; d->f[MF_hs0 + k][b] = (T)m->g_size[g][k]; }
+      for (int k = 0; k < 9; k++) d->f[MF_hR0 + k][b] = (T)R[k];
+    }
+  }
+  d->gravity = (T)m->gravity; d->solref_tc = (T)m->solref[0]; d->solref_dr = (T)m->solref[1];
+  for (int k = 0; k < 5; k++) d->solimp[k] = (T)m->solimp[k];
+  d->ground_friction = (T)m->ground_friction; d->finger_length = (T)m->finger_length; d->segment_length = (T)m->segment_length;
+  d->EI = (T)m->EI; d->clearance = (T)m->fingertip_clearance;
+  d->hook_length = (T)m->hook_length; d->hook_angle_deg = (T)m->hook_angle_deg; d->finger_width = (T)m->finger_width;
+  for (int f = 0; f < 3; f++) { d->tip_lane[f] = m->tip_body[f]; d->finger_lane[f] = m->finger_body[f]; for (int k = 0; k < 9; k++) d->tip_mat[f][k] = (T)m->tip_mat[f][k]; }
+  return 0;
+}
+
+// MjClass::configure_settings action table + Settings::update_sensor_settings
+// (src/mjclass.cpp:108-141, 5236-5265, quirk Q11)
+static int build_settings(const GmjSettings* s, DevSettings* d) {
+  memset(d, 0, sizeof(*d));
+  d->s = *s;
+  int n = 0, cont = (int)s->general[GS_continous_actions];
+  for (int a = 0; a < GACT_COUNT; a++) {
+    if (!s->action[a][GAF_in_use]) continue;
+    if (cont) d->action_options[n++] = 3 * a + 2;
+    else { d->action_options[n++] = 3 * a; d->action_options[n++] = 3 * a + 1; }
+  }
+  if (s->general[GS_use_termination_action]) d->action_options[n++] = 3 * GACT_COUNT;
+  d->n_actions = n;
+  double tps = s->general[GS_mujoco_timestep] * (int)s->general[GS_sim_steps_per_action];
+  for (int k = 0; k < GSEN_COUNT; k++) {
+    int is_state = (k == GSEN_motor_state || k == GSEN_base_XY || k == GSEN_base_Z || k == GSEN_base_yaw || k == GSEN_cartesian);
+    if (is_state) { d->prev_steps[k] = (int)s->general[GS_state_n_prev_steps]; d->readings_per_step[k] = 1; }
+    else {
+      d->prev_steps[k] = (int)s->general[GS_sensor_n_prev_steps];
+      float t = (float)tps, rr = (float)s->sensor[k][GSF_read_rate];
+      double rs = t * rr;
+      d->readings_per_step[k] = (int)floor(rs);
+    }
+    if (1 + d->prev_steps[k] * d->readings_per_step[k] > GMJ_WIN) FAIL("sensor history deeper than the device ring (GMJ_WIN)");
+  }
+  // observation length (src/mjclass.cpp:1700-1959)
+  int smode = (int)s->general[GS_sensor_sample_mode], tmode = (int)s->general[GS_state_sample_mode];
+  if (tmode == GSM_scaled_change_sq) { smode = GSM_scaled_change_sq; tmode = GSM_sign; }
+  auto len = [&](int sen, int mode) { return mode == GSM_raw ? d->prev_steps[sen] * d->readings_per_step[sen] : 2 * d->prev_steps[sen] + 1; };
+  int no = 0;
+  if (s->sensor[GSEN_bending_gauge][GSF_in_use]) no += 3 * len(GSEN_bending_gauge, smode);
+  if (s->sensor[GSEN_axial_gauge][GSF_in_use]) no += 3 * len(GSEN_axial_gauge, smode);
+  if (s->sensor[GSEN_palm][GSF_in_use]) no += len(GSEN_palm, smode);
+  if (s->sensor[GSEN_wrist_XY][GSF_in_use]) no += 2 * len(GSEN_wrist_XY, smode);
+  if (s->sensor[GSEN_wrist_Z][GSF_in_use]) no += len(GSEN_wrist_XY, smode);
+  if (s->sensor[GSEN_motor_state][GSF_in_use]) no += 3 * len(GSEN_motor_state, tmode);
+  if (s->sensor[GSEN_base_XY][GSF_in_use]) no += 2 * len(GSEN_base_XY, tmode);
+  if (s->sensor[GSEN_base_Z][GSF_in_use]) no += len(GSEN_base_Z, tmode);
+  if (s->sensor[GSEN_base_yaw][GSF_in_use]) no += len(GSEN_base_yaw, tmode);
+  if (s->sensor[GSEN_cartesian][GSF_in_use]) no += 12 * len(GSEN_cartesian, GSM_change);
+  if (no > GMJ_MAX_OBS) FAIL("observation longer than GMJ_MAX_OBS");
+  d->n_obs = no;
+  return 0;
+}

@@ -1,0 +1,186 @@
+// gmj_device.cuh -- device-side data layout and small math helpers for the batched gripper env.
+//
+// One environment per warp. Lane i owns gripper dof/body i in the reference order
+// (include/gmj_types.h): lane 0 = base slide, finger f occupies lanes fb..fb+N+1 with
+// fb = 1 + f*(N+2) (prismatic, revolute, N segment hinges), lane 3N+7 = palm. The free object
+// (6 dofs) is replicated in every lane. Per-env state lives in one contiguous block of HBM
+// (env-major), so a warp loads/stores its environment with coalesced accesses.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/gmj_types.h"
+
+#define GMJ_FULL 0xffffffffu
+#define GMJ_WIN 8            // ring depth kept per sensor stream (reference keeps 1000, reads <= 7)
+#define GMJ_RMAX 48          // constraint rows per env per substep (== GMJ_MAXROW)
+#define GMJ_NSTREAM_F 8      // normalised force streams: gauge1-3, axial1-3, palm, wristZ
+#define GMJ_NSTREAM_S 7      // state streams: motor x,y,z, base x,y, base z, yaw
+#define GMJ_NSTREAM_C 12     // cartesian contact streams (MAT)
+#define GMJ_NSTREAM (GMJ_NSTREAM_F + GMJ_NSTREAM_S + GMJ_NSTREAM_C)
+
+// luke::Gripper motor-space state (src/gripper.h)
+struct DevGripper { double x, y, z, th; int sx, sy, sz, pad; };
+
+// per-env persistent state (one block per env in HBM)
+template <typename T>
+struct EnvState {
+  T qpos[40];                 // [0,B) gripper joints; [32,39) object pos(3)+quat(4)
+  T qvel[40];                 // [0,B) gripper; [32,38) object lin(3 world)+ang(3 body)
+  T fprev[GMJ_RMAX];          // PGS warm start
+  T weld_anchor[8];           // joint value at weld activation (7 used)
+  T obj[20];                  // type,size3,round,quat4,mass,inertia3,friction,z_rest,bbox3
+  double time, last_step_time;
+  double last_read_time[4];   // bending, axial, palm, wristZ
+  DevGripper tend, tnext;     // target_.end / target_.next
+  double base_x, base_y, base_z, base_yaw;
+  double start_z;
+  float win[GMJ_NSTREAM][GMJ_WIN];
+  int win_i[GMJ_NSTREAM];
+  float si_latest[5];         // latest SI readings: gauge1-3, palm, wristZ
+  float rand_mu[GSEN_COUNT][3];
+  float ev_value[GBE_COUNT + GLE_COUNT];
+  float ev_last[GBE_COUNT + GLE_COUNT];
+  int ev_row[GBE_COUNT + GLE_COUNT];
+  int ev_abs[GBE_COUNT + GLE_COUNT];
+  float cumulative_reward, peak_lateral, last_reward, wrist_z;
+  int num_action_steps, termination_sent, unstable, has_object;
+  int weld_on, old_moving, nrow_prev, last_done;
+  uint32_t rng_ctr, env_id, episode, obj_index;
+  unsigned long long st_contacts, st_rows, st_iters, st_substeps;
+  unsigned int st_unstable, st_overflow, pad0, pad1;
+};
+
+// model constants, lane-major [field][32] so a warp reads each field conflict-free
+enum {
+  MF_parent = 0, MF_jtype, MF_depth, MF_fb, MF_local, MF_group,
+  MF_pos0, MF_pos1, MF_pos2,
+  MF_R0, MF_R1, MF_R2, MF_R3, MF_R4, MF_R5, MF_R6, MF_R7, MF_R8,
+  MF_ax0, MF_ax1, MF_ax2,
+  MF_mass, MF_ip0, MF_ip1, MF_ip2,
+  MF_ixx, MF_iyy, MF_izz, MF_ixy, MF_ixz, MF_iyz,
+  MF_stiff, MF_damp, MF_lo, MF_hi, MF_qpos0, MF_kp, MF_kd, MF_tsel,
+  // primary collision geom of the body (segment box / palm cylinder) and the hook plate
+  MF_gtype, MF_gp0, MF_gp1, MF_gp2, MF_gs0, MF_gs1, MF_gs2, MF_gfric, MF_gcls,
+  MF_gR0, MF_gR1, MF_gR2, MF_gR3, MF_gR4, MF_gR5, MF_gR6, MF_gR7, MF_gR8,
+  MF_htype, MF_hp0, MF_hp1, MF_hp2, MF_hs0, MF_hs1, MF_hs2,
+  MF_hR0, MF_hR1, MF_hR2, MF_hR3, MF_hR4, MF_hR5, MF_hR6, MF_hR7, MF_hR8,
+  MF_COUNT
+};
+
+template <typename T>
+struct DevModel {
+  T f[MF_COUNT][32];
+  int N, B, NL, palm_lane;
+  T gravity, solref_tc, solref_dr, solimp[5];
+  T ground_friction, finger_length, segment_length, EI, clearance, zref;
+  T hook_length, hook_angle_deg, finger_width;
+  int tip_lane[3], finger_lane[3];
+  T tip_mat[3][9];
+};
+
+struct DevSettings {
+  GmjSettings s;
+  int n_actions, action_options[32];
+  int prev_steps[GSEN_COUNT], readings_per_step[GSEN_COUNT];
+  int n_obs;
+};
+
+// ------------------------------------------------------------------ vec helpers
+template <typename T> struct V3 { T x, y, z; };
+template <typename T> __device__ __forceinline__ V3<T> mk(T x, T y, T z) { V3<T> r; r.x = x; r.y = y; r.z = z; return r; }
+template <typename T> __device__ __forceinline__ V3<T> operator+(V3<T> a, V3<T> b) { return mk<T>(a.x + b.x, a.y + b.y, a.z + b.z); }
+template <typename T> __device__ __forceinline__ V3<T> operator-(V3<T> a, V3<T> b) { return mk<T>(a.x - b.x, a.y - b.y, a.z - b.z); }
+template <typename T> __device__ __forceinline__ V3<T> operator*(V3<T> a, T s) { return mk<T>(a.x * s, a.y * s, a.z * s); }
+template <typename T> __device__ __forceinline__ T dot(V3<T> a, V3<T> b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+template <typename T> __device__ __forceinline__ V3<T> cross(V3<T> a, V3<T> b) {
+  return mk<T>(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+template <typename T> __device__ __forceinline__ V3<T> shfl3(V3<T> v, int src) {
+  return mk<T>(__shfl_sync(GMJ_FULL, v.x, src), __shfl_sync(GMJ_FULL, v.y, src), __shfl_sync(GMJ_FULL, v.z, src));
+}
+template <typename T> __device__ __forceinline__ V3<T> shflup3(V3<T> v, int d) {
+  return mk<T>(__shfl_up_sync(GMJ_FULL, v.x, d), __shfl_up_sync(GMJ_FULL, v.y, d), __shfl_up_sync(GMJ_FULL, v.z, d));
+}
+template <typename T> __device__ __forceinline__ V3<T> shfldn3(V3<T> v, int d) {
+  return mk<T>(__shfl_down_sync(GMJ_FULL, v.x, d), __shfl_down_sync(GMJ_FULL, v.y, d), __shfl_down_sync(GMJ_FULL, v.z, d));
+}
+// row-major 3x3
+template <typename T> struct M3 { T m[9]; };
+template <typename T> __device__ __forceinline__ V3<T> mul(const M3<T>& R, V3<T> v) {
+  return mk<T>(R.m[0] * v.x + R.m[1] * v.y + R.m[2] * v.z, R.m[3] * v.x + R.m[4] * v.y + R.m[5] * v.z,
+               R.m[6] * v.x + R.m[7] * v.y + R.m[8] * v.z);
+}
+template <typename T> __device__ __forceinline__ V3<T> mulT(const M3<T>& R, V3<T> v) {
+  return mk<T>(R.m[0] * v.x + R.m[3] * v.y + R.m[6] * v.z, R.m[1] * v.x + R.m[4] * v.y + R.m[7] * v.z,
+               R.m[2] * v.x + R.m[5] * v.y + R.m[8] * v.z);
+}
+template <typename T> __device__ __forceinline__ M3<T> mul(const M3<T>& A, const M3<T>& B) {
+  M3<T> o;
+#pragma unroll
+  for (int r = 0; r < 3; r++)
+#pragma unroll
+    for (int c = 0; c < 3; c++) o.m[3 * r + c] = A.m[3 * r] * B.m[c] + A.m[3 * r + 1] * B.m[3 + c] + A.m[3 * r + 2] * B.m[6 + c];
+  return o;
+}
+template <typename T> __device__ __forceinline__ M3<T> shflM(const M3<T>& A, int src) {
+  M3<T> o;
+#pragma unroll
+  for (int k = 0; k < 9; k++) o.m[k] = __shfl_sync(GMJ_FULL, A.m[k], src);
+  return o;
+}
+template <typename T> __device__ __forceinline__ M3<T> quat2mat(T w, T x, T y, T z) {
+  M3<T> R;
+  R.m[0] = 1 - 2 * (y * y + z * z); R.m[1] = 2 * (x * y - w * z); R.m[2] = 2 * (x * z + w * y);
+  R.m[3] = 2 * (x * y + w * z); R.m[4] = 1 - 2 * (x * x + z * z); R.m[5] = 2 * (y * z - w * x);
+  R.m[6] = 2 * (x * z - w * y); R.m[7] = 2 * (y * z + w * x); R.m[8] = 1 - 2 * (x * x + y * y);
+  return R;
+}
+template <typename T> __device__ __forceinline__ void sincosT(T t, T* s, T* c);
+template <> __device__ __forceinline__ void sincosT<float>(float t, float* s, float* c) { sincosf(t, s, c); }
+template <> __device__ __forceinline__ void sincosT<double>(double t, double* s, double* c) { sincos(t, s, c); }
+template <typename T> __device__ __forceinline__ T sqrtT(T x);
+template <> __device__ __forceinline__ float sqrtT<float>(float x) { return sqrtf(x); }
+template <> __device__ __forceinline__ double sqrtT<double>(double x) { return sqrt(x); }
+template <typename T> __device__ __forceinline__ T absT(T x) { return x < 0 ? -x : x; }
+template <typename T> __device__ __forceinline__ T maxT(T a, T b) { return a > b ? a : b; }
+template <typename T> __device__ __forceinline__ T minT(T a, T b) { return a < b ? a : b; }
+template <typename T> __device__ __forceinline__ T powT(T a, T b);
+template <> __device__ __forceinline__ float powT<float>(float a, float b) { return powf(a, b); }
+template <> __device__ __forceinline__ double powT<double>(double a, double b) { return pow(a, b); }
+
+template <typename T> __device__ __forceinline__ M3<T> rot_axis(V3<T> a, T t) {
+  T s, c; sincosT<T>(t, &s, &c);
+  T v = 1 - c;
+  M3<T> R;
+  R.m[0] = c + a.x * a.x * v; R.m[1] = a.x * a.y * v - a.z * s; R.m[2] = a.x * a.z * v + a.y * s;
+  R.m[3] = a.y * a.x * v + a.z * s; R.m[4] = c + a.y * a.y * v; R.m[5] = a.y * a.z * v - a.x * s;
+  R.m[6] = a.z * a.x * v - a.y * s; R.m[7] = a.z * a.y * v + a.x * s; R.m[8] = c + a.z * a.z * v;
+  return R;
+}
+template <typename T> __device__ __forceinline__ V3<T> normalized(V3<T> a) {
+  T l = sqrtT<T>(dot(a, a));
+  return l > 0 ? a * (T(1) / l) : a;
+}
+template <typename T> __device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(GMJ_FULL, v, o);
+  return v;
+}
+template <typename T> __device__ __forceinline__ T warp_max(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { T u = __shfl_xor_sync(GMJ_FULL, v, o); v = v > u ? v : u; }
+  return v;
+}
+
+// Philox4x32-10, first output word; identical to the oracle's generator (oracle/env.c)
+__device__ __forceinline__ uint32_t philox_first(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; r++) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  return c0;
+}

@@ -1,0 +1,712 @@
+// gmj_physics.cuh -- one physics substep of one environment, executed by one warp.
+//
+// Replaces luke::step = mj_step1 ; control ; mj_step2 (src/myfunctions.cpp:1873-1898) for the
+// gripper scene class. Pipeline (same semantics as MuJoCo's default options):
+//   kinematics (level loop over the tree, parent pose by warp shuffle)
+//   spatial inertias / velocities about a fixed reference point; prefix (velocity, bias
+//   acceleration) and suffix (composite inertia, force) scans inside each finger chain
+//   tree-sparse mass matrix: one dense (N+2)x(N+2) block per finger + base arrow
+//   LDL^T with the base ordered last (no fill-in), rows of L held in registers
+//   collision: lane-per-geom MPR against the object + closed-form plane contacts
+//   constraint rows (welds, limits, pyramidal contacts) stored WHITENED, W = D^-1/2 L^-1 J^T,
+//   so A = W W^T and no second copy (M^-1 J^T) is kept
+//   dual projected Gauss-Seidel, one lane per row, warm-started
+//   Euler with implicit joint damping through a second factorisation (M + h D)
+#pragma once
+#include "gmj_collide.cuh"
+#include "gmj_tail.cuh"
+
+#define GMJ_WS 41   // row stride of W (odd: conflict-free when lanes walk rows)
+#define GMJ_AS 49   // row stride of A
+
+template <typename T, int N>
+struct WarpShared {
+  EnvState<T> e;
+  WarpAux<T> ax;
+  T W[GMJ_RMAX + 1][GMJ_WS];        // whitened rows; row nrow holds the whitened smooth force
+  T A[GMJ_RMAX][GMJ_AS];            // A[r][c], c = nrow column holds W_r . w_s
+  T L2[3][N + 2][N + 3];            // second factor, for column access in the back substitution
+  T qfk[40];                        // qpos of the last kinematics pass (weld anchors)
+  T rpos[GMJ_RMAX], rjv[GMJ_RMAX], rmu[GMJ_RMAX];
+  int rtype[GMJ_RMAX], rfirst[GMJ_RMAX], rlane[GMJ_RMAX];
+};
+
+enum { ROW_EQ = 0, ROW_LIMIT = 1, ROW_CONTACT = 2 };
+
+template <typename T> struct Sp { V3<T> w, v; };           // spatial motion (w; v) or force (n; f)
+template <typename T> __device__ __forceinline__ Sp<T> operator+(Sp<T> a, Sp<T> b) { Sp<T> r; r.w = a.w + b.w; r.v = a.v + b.v; return r; }
+template <typename T> __device__ __forceinline__ Sp<T> operator*(Sp<T> a, T s) { Sp<T> r; r.w = a.w * s; r.v = a.v * s; return r; }
+template <typename T> __device__ __forceinline__ T spdot(Sp<T> a, Sp<T> b) { return dot(a.w, b.w) + dot(a.v, b.v); }
+template <typename T> __device__ __forceinline__ Sp<T> spshfl(Sp<T> a, int src) { Sp<T> r; r.w = shfl3(a.w, src); r.v = shfl3(a.v, src); return r; }
+template <typename T> __device__ __forceinline__ Sp<T> spup(Sp<T> a, int d) { Sp<T> r; r.w = shflup3(a.w, d); r.v = shflup3(a.v, d); return r; }
+template <typename T> __device__ __forceinline__ Sp<T> spdn(Sp<T> a, int d) { Sp<T> r; r.w = shfldn3(a.w, d); r.v = shfldn3(a.v, d); return r; }
+template <typename T> __device__ __forceinline__ Sp<T> crossm(Sp<T> v, Sp<T> s) { Sp<T> r; r.w = cross(v.w, s.w); r.v = cross(v.w, s.v) + cross(v.v, s.w); return r; }
+template <typename T> __device__ __forceinline__ Sp<T> crossf(Sp<T> v, Sp<T> f) { Sp<T> r; r.w = cross(v.w, f.w) + cross(v.v, f.v); r.v = cross(v.w, f.v); return r; }
+// spatial inertia about the reference point: mass, first moment h = m c, symmetric I (xx yy zz xy xz yz)
+template <typename T> struct SpI { T m; V3<T> h; T I[6]; };
+template <typename T> __device__ __forceinline__ V3<T> symmul(const T* I, V3<T> v) {
+  return mk<T>(I[0] * v.x + I[3] * v.y + I[4] * v.z, I[3] * v.x + I[1] * v.y + I[5] * v.z, I[4] * v.x + I[5] * v.y + I[2] * v.z);
+}
+template <typename T> __device__ __forceinline__ Sp<T> spimul(const SpI<T>& I, Sp<T> s) {
+  Sp<T> r; r.w = symmul(I.I, s.w) + cross(I.h, s.v); r.v = s.v * I.m + cross(s.w, I.h); return r;
+}
+template <typename T> __device__ __forceinline__ SpI<T> spiadd(SpI<T> a, const SpI<T>& b) {
+  a.m += b.m; a.h = a.h + b.h;
+#pragma unroll
+  for (int k = 0; k < 6; k++) a.I[k] += b.I[k];
+  return a;
+}
+template <typename T> __device__ __forceinline__ SpI<T> spishfl_dn(const SpI<T>& a, int d) {
+  SpI<T> r; r.m = __shfl_down_sync(GMJ_FULL, a.m, d); r.h = shfldn3(a.h, d);
+#pragma unroll
+  for (int k = 0; k < 6; k++) r.I[k] = __shfl_down_sync(GMJ_FULL, a.I[k], d);
+  return r;
+}
+template <typename T> __device__ __forceinline__ SpI<T> spishfl(const SpI<T>& a, int src) {
+  SpI<T> r; r.m = __shfl_sync(GMJ_FULL, a.m, src); r.h = shfl3(a.h, src);
+#pragma unroll
+  for (int k = 0; k < 6; k++) r.I[k] = __shfl_sync(GMJ_FULL, a.I[k], src);
+  return r;
+}
+
+// lane topology (compile-time arithmetic, no loads)
+template <int N> struct Topo {
+  static constexpr int NL = N + 2, B = 3 * N + 8, PALM = 3 * N + 7;
+  int lane, fb, local, depth, parent; bool act, chain, hinge;
+  __device__ __forceinline__ Topo(int l) {
+    lane = l; act = l < B;
+    if (l == 0) { fb = 0; local = 0; depth = 0; parent = 0; chain = false; hinge = false; }
+    else if (l < PALM) { int f = (l - 1) / NL; local = (l - 1) - f * NL; fb = 1 + f * NL; depth = local + 1; parent = local == 0 ? 0 : l - 1; chain = true; hinge = local > 0; }
+    else if (l == PALM) { fb = PALM; local = 0; depth = 1; parent = 0; chain = false; hinge = false; }
+    else { fb = l; local = 0; depth = 99; parent = 0; chain = false; hinge = false; }
+  }
+};
+
+// LDL^T of the block-arrow mass matrix. In: Mrow[k] = M[lane][fb+k] (k <= local), Mb = M[lane][base],
+// lane 0: Mrow[0] = M[0][0]. Out: Mrow[k<local] = L entries, D = pivot of this lane, lb = L[base][lane].
+template <typename T, int N>
+__device__ __forceinline__ void ldl_factor(const Topo<N>& tp, T* Mrow, T Mb, T& D, T& lb) {
+  constexpr int NL = N + 2;
+#pragma unroll
+  for (int k = 0; k < NL - 1; k++) {
+    T Dk = __shfl_sync(GMJ_FULL, Mrow[k], tp.fb + k);
+    T Mbk = __shfl_sync(GMJ_FULL, Mb, tp.fb + k);
+    T inv = T(1) / Dk;
+    bool below = tp.chain && tp.local > k;
+    T mk_pre = Mrow[k];
+    T l = below ? mk_pre * inv : T(0);
+#pragma unroll
+    for (int j = k + 1; j < NL; j++) {
+      T mjk = __shfl_sync(GMJ_FULL, mk_pre, tp.fb + j);
+      if (below && tp.local >= j) Mrow[j] -= l * mjk;
+    }
+    if (below) { Mb -= (Mbk * inv) * mk_pre; Mrow[k] = l; }
+  }
+  // pivots
+  T d = T(1);
+#pragma unroll
+  for (int k = 0; k < NL; k++) if (tp.local == k) d = Mrow[k];
+  T contrib = (tp.lane != 0 && tp.act) ? Mb * Mb / d : T(0);
+  T s = warp_sum(contrib);
+  if (tp.lane == 0) { D = Mrow[0] - s; lb = 0; }
+  else { D = d; lb = tp.act ? Mb / d : T(0); }
+}
+
+// x <- L^-1 x (lane-distributed)
+template <typename T, int N>
+__device__ __forceinline__ T ldl_fwd(const Topo<N>& tp, const T* Lrow, T lb, T x) {
+  constexpr int NL = N + 2;
+#pragma unroll
+  for (int k = 0; k < NL - 1; k++) {
+    T xk = __shfl_sync(GMJ_FULL, x, tp.fb + k);
+    if (tp.chain && tp.local > k) x -= Lrow[k] * xk;
+  }
+  T s = warp_sum((tp.lane != 0 && tp.act) ? lb * x : T(0));
+  if (tp.lane == 0) x -= s;
+  return x;
+}
+// y = L x
+template <typename T, int N>
+__device__ __forceinline__ T ldl_mulL(const Topo<N>& tp, const T* Lrow, T lb, T x) {
+  constexpr int NL = N + 2;
+  T acc = x;
+#pragma unroll
+  for (int k = 0; k < NL - 1; k++) {
+    T xk = __shfl_sync(GMJ_FULL, x, tp.fb + k);
+    if (tp.chain && tp.local > k) acc += Lrow[k] * xk;
+  }
+  T s = warp_sum((tp.lane != 0 && tp.act) ? lb * x : T(0));
+  if (tp.lane == 0) acc += s;
+  return acc;
+}
+
+template <typename T> __device__ __forceinline__ T impedance(const T* solimp, T pos) {
+  T d0 = solimp[0], dw = solimp[1], width = solimp[2], mid = solimp[3], power = solimp[4];
+  T x = absT<T>(pos) / width;
+  if (x >= 1) return dw;
+  if (x <= 0) return d0;
+  T y;
+  if (x <= mid) y = powT<T>(x / mid, power) * mid;
+  else y = 1 - powT<T>((1 - x) / (1 - mid), power) * (1 - mid);
+  return d0 + y * (dw - d0);
+}
+
+// ---------------------------------------------------------------------------------------------
+// emit one constraint row: whiten the lane-distributed gripper part, store row + meta
+template <typename T, int N>
+__device__ __forceinline__ void emit_row(WarpShared<T, N>& ws, const Topo<N>& tp, const T* Lrow, T lb, T rsq,
+                                         const T* rsqo, int r, T Jl, const T* Jo, int type, T pos, T jv, T mu,
+                                         int first, int jl) {
+  T x = ldl_fwd<T, N>(tp, Lrow, lb, Jl) * rsq;
+  ws.W[r][tp.lane] = tp.act ? x : T(0);
+  if (tp.lane == 0) {
+#pragma unroll
+    for (int k = 0; k < 6; k++) ws.W[r][32 + k] = Jo[k] * rsqo[k];
+    ws.rtype[r] = type; ws.rpos[r] = pos; ws.rjv[r] = jv; ws.rmu[r] = mu; ws.rfirst[r] = first; ws.rlane[r] = jl;
+  }
+}
+
+// point Jacobian entry of this lane's dof for a point p on gripper body `bl` (lane index) projected
+// on direction d: d . (a x (p - anchor)) for hinges, d . a for slides, 0 if the dof is not an ancestor
+template <typename T, int N>
+__device__ __forceinline__ T jac_entry(const Topo<N>& tp, int bl, V3<T> p, V3<T> d, V3<T> aw, V3<T> anchor) {
+  if (bl < 0 || !tp.act) return T(0);
+  bool anc;
+  if (tp.lane == 0) anc = true;
+  else if (tp.lane == Topo<N>::PALM) anc = (bl == Topo<N>::PALM);
+  else anc = (bl >= tp.fb && bl < tp.fb + Topo<N>::NL && bl >= tp.lane);
+  if (!anc) return T(0);
+  return tp.hinge ? dot(d, cross(aw, p - anchor)) : dot(d, aw);
+}
+
+template <typename T, int N>
+__device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, const DevSettings& S, int lane, double dtd, T tip_force) {
+  const T dt = (T)dtd;
+  constexpr int NL = N + 2, B = 3 * N + 8, PALM = 3 * N + 7;
+  const Topo<N> tp(lane);
+  EnvState<T>& e = ws.e;
+  const T gz = -M.zref;                                   // ground plane height in shifted coordinates
+
+  // ------------------------------------------------------------------ kinematics
+  T q = tp.act ? e.qpos[lane] : T(0), qd = tp.act ? e.qvel[lane] : T(0);
+  ws.qfk[lane] = q;
+  M3<T> Rl; V3<T> pl = mk<T>(M.f[MF_pos0][lane], M.f[MF_pos1][lane], M.f[MF_pos2][lane]);
+  V3<T> axl = mk<T>(M.f[MF_ax0][lane], M.f[MF_ax1][lane], M.f[MF_ax2][lane]);
+#pragma unroll
+  for (int k = 0; k < 9; k++) Rl.m[k] = M.f[MF_R0 + k][lane];
+  M3<T> R; V3<T> p = mk<T>(0, 0, 0), aw = mk<T>(0, 0, 1), anchor = mk<T>(0, 0, 0);
+#pragma unroll
+  for (int k = 0; k < 9; k++) R.m[k] = (k % 4 == 0) ? T(1) : T(0);
+#pragma unroll
+  for (int d = 0; d <= NL; d++) {
+    M3<T> Rp = shflM(R, tp.parent);
+    V3<T> pp = shfl3(p, tp.parent);
+    if (tp.depth == d) {
+      M3<T> R0; V3<T> P0;
+      if (d == 0) { R0 = Rl; P0 = pl; } else { R0 = mul(Rp, Rl); P0 = pp + mul(Rp, pl); }
+      aw = mul(R0, axl); anchor = P0;
+      if (!tp.hinge) { R = R0; p = P0 + aw * q; } else { R = mul(R0, rot_axis(axl, q)); p = P0; }
+    }
+  }
+  // local force frames for the tally (xmat of finger_i and palm)
+  if (tp.chain && tp.local == 1) { int f = (lane - 1) / NL;
+#pragma unroll
+    for (int k = 0; k < 9; k++) ws.ax.fingerR[f][k] = R.m[k]; }
+  if (lane == PALM) {
+#pragma unroll
+    for (int k = 0; k < 9; k++) ws.ax.palmR[k] = R.m[k]; }
+  // object (replicated in every lane)
+  V3<T> po = mk<T>(e.qpos[32], e.qpos[33], e.qpos[34] - M.zref);
+  M3<T> Ro;
+  { T a = e.qpos[35], b = e.qpos[36], c = e.qpos[37], d = e.qpos[38];
+    T l = T(1) / sqrtT<T>(a * a + b * b + c * c + d * d);
+    Ro = quat2mat<T>(a * l, b * l, c * l, d * l); }
+  V3<T> vo = mk<T>(e.qvel[32], e.qvel[33], e.qvel[34]), wo = mk<T>(e.qvel[35], e.qvel[36], e.qvel[37]);
+  const bool has_obj = e.has_object != 0;
+  const T om = e.obj[9];
+  const V3<T> oI = mk<T>(e.obj[10], e.obj[11], e.obj[12]);
+
+  // ------------------------------------------------------------------ spatial quantities
+  T mass = tp.act ? M.f[MF_mass][lane] : T(0);
+  V3<T> c = p + mul(R, mk<T>(M.f[MF_ip0][lane], M.f[MF_ip1][lane], M.f[MF_ip2][lane]));
+  SpI<T> I;
+  {
+    T ib[6] = { M.f[MF_ixx][lane], M.f[MF_iyy][lane], M.f[MF_izz][lane], M.f[MF_ixy][lane], M.f[MF_ixz][lane], M.f[MF_iyz][lane] };
+    M3<T> Ib; Ib.m[0] = ib[0]; Ib.m[4] = ib[1]; Ib.m[8] = ib[2]; Ib.m[1] = Ib.m[3] = ib[3]; Ib.m[2] = Ib.m[6] = ib[4]; Ib.m[5] = Ib.m[7] = ib[5];
+    M3<T> t = mul(R, Ib);
+    // Iw = t R^T (symmetric)
+    T Iw[6];
+    Iw[0] = t.m[0] * R.m[0] + t.m[1] * R.m[1] + t.m[2] * R.m[2];
+    Iw[1] = t.m[3] * R.m[3] + t.m[4] * R.m[4] + t.m[5] * R.m[5];
+    Iw[2] = t.m[6] * R.m[6] + t.m[7] * R.m[7] + t.m[8] * R.m[8];
+    Iw[3] = t.m[0] * R.m[3] + t.m[1] * R.m[4] + t.m[2] * R.m[5];
+    Iw[4] = t.m[0] * R.m[6] + t.m[1] * R.m[7] + t.m[2] * R.m[8];
+    Iw[5] = t.m[3] * R.m[6] + t.m[4] * R.m[7] + t.m[5] * R.m[8];
+    T cc = dot(c, c);
+    I.m = mass; I.h = c * mass;
+    I.I[0] = Iw[0] + mass * (cc - c.x * c.x); I.I[1] = Iw[1] + mass * (cc - c.y * c.y); I.I[2] = Iw[2] + mass * (cc - c.z * c.z);
+    I.I[3] = Iw[3] - mass * c.x * c.y; I.I[4] = Iw[4] - mass * c.x * c.z; I.I[5] = Iw[5] - mass * c.y * c.z;
+    if (!tp.act) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) I.I[k] = 0;
+    }
+  }
+  Sp<T> Sj;
+  if (!tp.act) { Sj.w = mk<T>(0, 0, 0); Sj.v = mk<T>(0, 0, 0); }
+  else if (!tp.hinge) { Sj.w = mk<T>(0, 0, 0); Sj.v = aw; }
+  else { Sj.w = aw; Sj.v = cross(anchor, aw); }
+  // velocities: inclusive prefix inside each chain, then add the base
+  Sp<T> v = Sj * qd;
+#pragma unroll
+  for (int off = 1; off < NL; off <<= 1) { Sp<T> t = spup(v, off); if (tp.chain && tp.local >= off) v = v + t; }
+  Sp<T> vbase = spshfl(v, 0);
+  if (lane != 0 && tp.act) v = v + vbase;
+  // bias accelerations
+  Sp<T> a = crossm(v, Sj) * qd;
+#pragma unroll
+  for (int off = 1; off < NL; off <<= 1) { Sp<T> t = spup(a, off); if (tp.chain && tp.local >= off) a = a + t; }
+  Sp<T> abase = spshfl(a, 0);
+  if (lane != 0 && tp.act) a = a + abase;
+  a.v.z += M.gravity;
+  // forces and composite inertias: inclusive suffix inside each chain, then gather into the base
+  Sp<T> f = spimul(I, a) + crossf(v, spimul(I, v));
+  SpI<T> Ic = I;
+#pragma unroll
+  for (int off = 1; off < NL; off <<= 1) {
+    Sp<T> tf = spdn(f, off); SpI<T> ti = spishfl_dn(Ic, off);
+    if (tp.chain && tp.local + off < NL) { f = f + tf; Ic = spiadd(Ic, ti); }
+  }
+  {
+    Sp<T> fs = f; SpI<T> is = Ic;
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+      int src = (r < 3) ? (1 + r * NL) : PALM;
+      Sp<T> tf = spshfl(f, src); SpI<T> ti = spishfl(Ic, src);
+      if (lane == 0) { fs = fs + tf; is = spiadd(is, ti); }
+    }
+    f = fs; Ic = is;
+  }
+  T bias = spdot(Sj, f);
+  // mass matrix rows: M[lane][fb+k] and coupling to the base
+  Sp<T> F = spimul(Ic, Sj);
+  T Mrow[NL];
+#pragma unroll
+  for (int k = 0; k < NL; k++) {
+    Sp<T> Sk = spshfl(Sj, tp.fb + k);
+    Mrow[k] = (k <= tp.local) ? spdot(Sk, F) : T(0);
+  }
+  Sp<T> Sb = spshfl(Sj, 0);
+  T Mb = (lane != 0 && tp.act) ? spdot(Sb, F) : T(0);
+
+  // ------------------------------------------------------------------ control + smooth forces
+  // luke::control_gripper / control_base (src/myfunctions.cpp:1965-2057)
+  T damp = tp.act ? M.f[MF_damp][lane] : T(0), stiff = tp.act ? M.f[MF_stiff][lane] : T(0);
+  T ctrl = 0;
+  {
+    int tsel = (int)M.f[MF_tsel][lane];
+    T tgt = 0;
+    if (tsel == 1) tgt = (T)e.base_z; else if (tsel == 2) tgt = (T)e.tnext.x; else if (tsel == 3) tgt = (T)e.tnext.th; else if (tsel == 4) tgt = (T)e.tnext.z;
+    if (tsel != 0) ctrl = -((q - tgt) * M.f[MF_kp][lane] + qd * M.f[MF_kd][lane]);
+  }
+  T tau = -bias + ctrl - stiff * q - damp * qd;
+  T wrist = ctrl - damp * qd - stiff * q;                 // lane 0: force sensor z (quirk Q3)
+  if (tip_force != T(0)) {
+    // calibration tip load on the last segment of each finger (src/myfunctions.cpp:1642-1727)
+    int fidx = tp.chain ? (lane - 1) / NL : 0;
+    int tl = M.tip_lane[fidx];
+    V3<T> ct = shfl3(c, tl);
+    V3<T> fv = mk<T>(-M.tip_mat[fidx][2] * tip_force, -M.tip_mat[fidx][5] * tip_force, -M.tip_mat[fidx][8] * tip_force);
+    Sp<T> fs; fs.w = cross(ct, fv); fs.v = fv;
+    if (tp.chain) tau += spdot(Sj, fs);
+    // base: all three fingers
+    T tb = 0;
+#pragma unroll
+    for (int ff = 0; ff < 3; ff++) {
+      V3<T> c2 = shfl3(c, M.tip_lane[ff]);
+      V3<T> f2 = mk<T>(-M.tip_mat[ff][2] * tip_force, -M.tip_mat[ff][5] * tip_force, -M.tip_mat[ff][8] * tip_force);
+      Sp<T> s2; s2.w = cross(c2, f2); s2.v = f2;
+      tb += spdot(Sj, s2);
+    }
+    if (lane == 0) tau += tb;
+  }
+  // object smooth force (free joint: world linear dofs, body-frame angular dofs)
+  T tauo[6], rsqo[6], Mo[6];
+  {
+    V3<T> Iw = mk<T>(oI.x * wo.x, oI.y * wo.y, oI.z * wo.z);
+    V3<T> gyr = cross(wo, Iw);
+    tauo[0] = 0; tauo[1] = 0; tauo[2] = has_obj ? -om * M.gravity : T(0);
+    tauo[3] = has_obj ? -gyr.x : T(0); tauo[4] = has_obj ? -gyr.y : T(0); tauo[5] = has_obj ? -gyr.z : T(0);
+    Mo[0] = Mo[1] = Mo[2] = has_obj ? om : T(1);
+    Mo[3] = has_obj ? oI.x : T(1); Mo[4] = has_obj ? oI.y : T(1); Mo[5] = has_obj ? oI.z : T(1);
+#pragma unroll
+    for (int k = 0; k < 6; k++) rsqo[k] = T(1) / sqrtT<T>(Mo[k]);
+  }
+
+  // ------------------------------------------------------------------ factorisations
+  T M2row[NL];
+#pragma unroll
+  for (int k = 0; k < NL; k++) M2row[k] = Mrow[k] + ((k == tp.local && tp.act) ? dt * damp : T(0));
+  T D, lb, D2, lb2;
+  ldl_factor<T, N>(tp, Mrow, Mb, D, lb);
+  ldl_factor<T, N>(tp, M2row, Mb, D2, lb2);
+  const T rsq = tp.act ? T(1) / sqrtT<T>(D) : T(0);
+  int bad = !(D > 0) && tp.act;
+  // second factor to shared memory for column access
+  if (tp.chain) { int fi = (lane - 1) / NL;
+#pragma unroll
+    for (int k = 0; k < NL; k++) ws.L2[fi][tp.local][k] = (k < tp.local) ? M2row[k] : T(0); }
+
+  // whitened smooth force w_s = D^-1/2 L^-1 tau
+  T wsm = ldl_fwd<T, N>(tp, Mrow, lb, tau) * rsq;
+  __syncwarp();
+
+  // ------------------------------------------------------------------ collision
+  int ncon = 0;
+  Shape<T> so;
+  so.type = (int)e.obj[0]; so.size = mk<T>(e.obj[1], e.obj[2], e.obj[3]); so.round = e.obj[4];
+  so.pos = po; so.R = mul(Ro, quat2mat<T>(e.obj[5], e.obj[6], e.obj[7], e.obj[8]));
+  const T ofric = e.obj[13];
+  auto add_contact = [&](V3<T> pos, V3<T> n, T dist, T mu, int b1, int c1, int b2, int c2, int slot) {
+    DevContact<T>& cn = ws.ax.con[slot];
+    cn.pos[0] = pos.x; cn.pos[1] = pos.y; cn.pos[2] = pos.z;
+    make_frame<T>(n, cn.frame);
+    cn.dist = dist; cn.mu = mu; cn.body1 = b1; cn.body2 = b2; cn.cls1 = c1; cn.cls2 = c2;
+    cn.force[0] = cn.force[1] = cn.force[2] = 0; cn.row = -1;
+  };
+  // (1) object vs ground: uniform work, lane 0 writes
+  if (has_obj) {
+    V3<T> pts[8]; T dd[8];
+    int n = plane_candidates<T>(so, gz, pts, dd);
+    T mu = maxT<T>(M.ground_friction, ofric);
+    for (int k = 0; k < 4 && k < n; k++) {
+      int best = -1;
+      for (int i = 0; i < n; i++) if (dd[i] < 0 && (best < 0 || dd[i] < dd[best])) best = i;
+      if (best < 0) break;
+      if (ncon < GMJ_MAXCON) {
+        if (lane == 0) { V3<T> pp = pts[best]; pp.z -= T(0.5) * dd[best]; add_contact(pp, mk<T>(0, 0, 1), dd[best], mu, -1, GMJ_CLS_GROUND, B, GMJ_CLS_OBJECT, ncon); }
+        ncon++;
+      }
+      dd[best] = 1;
+    }
+  }
+  // per-lane geoms: primary (segment plate / palm cylinder) and hook plate on the tip lanes
+  Shape<T> sg, sh;
+  const int gtype = tp.act ? (int)M.f[MF_gtype][lane] : -1, htype = tp.act ? (int)M.f[MF_htype][lane] : -1;
+  const int gcls = (int)M.f[MF_gcls][lane];
+  const T gfric = M.f[MF_gfric][lane];
+  {
+    M3<T> Rg, Rh;
+#pragma unroll
+    for (int k = 0; k < 9; k++) { Rg.m[k] = M.f[MF_gR0 + k][lane]; Rh.m[k] = M.f[MF_hR0 + k][lane]; }
+    sg.type = gtype; sg.round = 0; sg.size = mk<T>(M.f[MF_gs0][lane], M.f[MF_gs1][lane], M.f[MF_gs2][lane]);
+    sg.pos = p + mul(R, mk<T>(M.f[MF_gp0][lane], M.f[MF_gp1][lane], M.f[MF_gp2][lane])); sg.R = mul(R, Rg);
+    sh.type = htype; sh.round = 0; sh.size = mk<T>(M.f[MF_hs0][lane], M.f[MF_hs1][lane], M.f[MF_hs2][lane]);
+    sh.pos = p + mul(R, mk<T>(M.f[MF_hp0][lane], M.f[MF_hp1][lane], M.f[MF_hp2][lane])); sh.R = mul(R, Rh);
+  }
+  // (2) gripper plates vs ground (rare): lanes with a vertex below the plane emit in lane order,
+  // primary geom first then the hook (== geom order of the model)
+  {
+    V3<T> pts[8]; T dd[8];
+    bool lowg = false, lowh = false;
+    if (gtype == GMJ_GEOM_BOX) { int n = plane_candidates<T>(sg, gz, pts, dd); for (int i = 0; i < n; i++) lowg |= dd[i] < 0; }
+    if (htype == GMJ_GEOM_BOX) { int n = plane_candidates<T>(sh, gz, pts, dd); for (int i = 0; i < n; i++) lowh |= dd[i] < 0; }
+    unsigned mg = __ballot_sync(GMJ_FULL, lowg), mh = __ballot_sync(GMJ_FULL, lowh);
+    unsigned any = mg | mh;
+    while (any) {
+      int src = __ffs(any) - 1; any &= any - 1;
+      for (int which = 0; which < 2; which++) {
+        if (!(((which == 0) ? mg : mh) >> src & 1)) continue;
+        int cnt = 0;
+        if (lane == src) {
+          const Shape<T>& s = which == 0 ? sg : sh;
+          int n = plane_candidates<T>(s, gz, pts, dd);
+          T mu = maxT<T>(M.ground_friction, gfric);
+          for (int k = 0; k < 4 && k < n; k++) {
+            int best = -1;
+            for (int i = 0; i < n; i++) if (dd[i] < 0 && (best < 0 || dd[i] < dd[best])) best = i;
+            if (best < 0) break;
+            if (ncon + cnt < GMJ_MAXCON) { V3<T> pp = pts[best]; pp.z -= T(0.5) * dd[best]; add_contact(pp, mk<T>(0, 0, 1), dd[best], mu, -1, GMJ_CLS_GROUND, lane, gcls, ncon + cnt); cnt++; }
+            dd[best] = 1;
+          }
+        }
+        ncon += __shfl_sync(GMJ_FULL, cnt, src);
+      }
+    }
+  }
+  // (3) object vs gripper geoms: one MPR query per lane (and a second pass for the hooks)
+  if (has_obj) {
+    T ro = shape_bound(so);
+    int hitg = 0, hith = 0; T depg = 0, deph = 0; V3<T> ng, nh, pg, ph;
+    // queries run in coordinates relative to the object centre (keeps FP32 resolution)
+    Shape<T> so0 = so; so0.pos = mk<T>(0, 0, 0);
+    if (gtype >= 0) {
+      V3<T> d = sg.pos - so.pos; T rr = ro + shape_bound(sg);
+      if (dot(d, d) <= rr * rr) { Shape<T> s0 = sg; s0.pos = d; hitg = mpr_penetration<T>(s0, so0, &depg, &ng, &pg); }
+    }
+    if (htype >= 0) {
+      V3<T> d = sh.pos - so.pos; T rr = ro + shape_bound(sh);
+      if (dot(d, d) <= rr * rr) { Shape<T> s0 = sh; s0.pos = d; hith = mpr_penetration<T>(s0, so0, &deph, &nh, &ph); }
+    }
+    unsigned mg = __ballot_sync(GMJ_FULL, hitg), mh = __ballot_sync(GMJ_FULL, hith);
+    unsigned any = mg | mh;
+    while (any) {
+      int src = __ffs(any) - 1; any &= any - 1;
+      if ((mg >> src) & 1) {
+        if (ncon < GMJ_MAXCON) { if (lane == src) add_contact(pg + so.pos, ng, -depg, maxT<T>(gfric, ofric), lane, gcls, B, GMJ_CLS_OBJECT, ncon); ncon++; }
+      }
+      if ((mh >> src) & 1) {
+        if (ncon < GMJ_MAXCON) { if (lane == src) add_contact(ph + so.pos, nh, -deph, maxT<T>(gfric, ofric), lane, gcls, B, GMJ_CLS_OBJECT, ncon); ncon++; }
+      }
+    }
+  }
+  __syncwarp();
+
+  // ------------------------------------------------------------------ constraint rows
+  int nr = 0;
+  const T zero6[6] = { 0, 0, 0, 0, 0, 0 };
+  // welds: joint `j` locked at its anchor; rows = world components of the joint axis
+  // (weld residual of MuJoCo restricted to the single joint between the two bodies)
+#pragma unroll 1
+  for (int id = 0; id < 7; id++) {
+    if (!((e.weld_on >> id) & 1)) continue;
+    int j = (id < 3) ? (1 + id * NL) : ((id < 6) ? (2 + (id - 3) * NL) : PALM);
+    V3<T> aj = shfl3(aw, j);
+    T qj = __shfl_sync(GMJ_FULL, q, j), qdj = __shfl_sync(GMJ_FULL, qd, j);
+    bool rev = (id >= 3 && id < 6);
+    T sgn = rev ? T(-1) : T(1);
+    T s1, c1; sincosT<T>(qj - e.weld_anchor[id], &s1, &c1);
+    T rho = rev ? s1 : (qj - e.weld_anchor[id]);
+    T comp[3] = { aj.x, aj.y, aj.z };
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+      if (comp[d] * comp[d] < T(1e-10)) continue;
+      if (nr >= GMJ_RMAX) break;
+      T Jl = (lane == j) ? sgn * comp[d] : T(0);
+      emit_row<T, N>(ws, tp, Mrow, lb, rsq, rsqo, nr, Jl, zero6, ROW_EQ, sgn * rho * comp[d], sgn * comp[d] * qdj, T(0), nr, j);
+      nr++;
+    }
+  }
+  // joint limits (margin 0)
+  {
+    T lo = q - M.f[MF_lo][lane], hi = M.f[MF_hi][lane] - q;
+    unsigned mlo = __ballot_sync(GMJ_FULL, tp.act && lo < 0), mhi = __ballot_sync(GMJ_FULL, tp.act && hi < 0);
+    unsigned any = mlo | mhi;
+    while (any) {
+      int j = __ffs(any) - 1; any &= any - 1;
+      T loj = __shfl_sync(GMJ_FULL, lo, j), hij = __shfl_sync(GMJ_FULL, hi, j), qdj = __shfl_sync(GMJ_FULL, qd, j);
+      if (((mlo >> j) & 1) && nr < GMJ_RMAX) { emit_row<T, N>(ws, tp, Mrow, lb, rsq, rsqo, nr, lane == j ? T(1) : T(0), zero6, ROW_LIMIT, loj, qdj, T(1), nr, j); nr++; }
+      if (((mhi >> j) & 1) && nr < GMJ_RMAX) { emit_row<T, N>(ws, tp, Mrow, lb, rsq, rsqo, nr, lane == j ? T(-1) : T(0), zero6, ROW_LIMIT, hij, -qdj, T(-1), nr, j); nr++; }
+    }
+  }
+  // contacts: pyramidal, condim 3 -> 4 rows each
+#pragma unroll 1
+  for (int cidx = 0; cidx < ncon; cidx++) {
+    if (nr + 4 > GMJ_RMAX) { ncon = cidx; break; }
+    DevContact<T>& cn = ws.ax.con[cidx];
+    V3<T> cp = mk<T>(cn.pos[0], cn.pos[1], cn.pos[2]);
+    T mu = cn.mu;
+    int b1 = cn.body1, b2 = cn.body2;
+    T Jc[3], Joc[3][6], jvc[3];
+#pragma unroll
+    for (int ax3 = 0; ax3 < 3; ax3++) {
+      V3<T> d = mk<T>(cn.frame[3 * ax3], cn.frame[3 * ax3 + 1], cn.frame[3 * ax3 + 2]);
+      T j2 = (b2 < B) ? jac_entry<T, N>(tp, b2, cp, d, aw, anchor) : T(0);
+      T j1 = jac_entry<T, N>(tp, b1, cp, d, aw, anchor);
+      Jc[ax3] = j2 - j1;
+      // object part (body2 == B): linear dofs world, angular dofs body frame
+#pragma unroll
+      for (int k = 0; k < 6; k++) Joc[ax3][k] = 0;
+      T jvo = 0;
+      if (b2 == B) {
+        Joc[ax3][0] = d.x; Joc[ax3][1] = d.y; Joc[ax3][2] = d.z;
+        V3<T> r = cp - po;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          V3<T> axk = mk<T>(Ro.m[k], Ro.m[3 + k], Ro.m[6 + k]);
+          Joc[ax3][3 + k] = dot(d, cross(axk, r));
+        }
+        jvo = Joc[ax3][0] * vo.x + Joc[ax3][1] * vo.y + Joc[ax3][2] * vo.z + Joc[ax3][3] * wo.x + Joc[ax3][4] * wo.y + Joc[ax3][5] * wo.z;
+      }
+      jvc[ax3] = warp_sum(Jc[ax3] * qd) + jvo;
+    }
+    if (lane == 0) cn.row = nr;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int t = 1 + (k >> 1); const T sg2 = (k & 1) ? -mu : mu;
+      T Jo[6];
+#pragma unroll
+      for (int i = 0; i < 6; i++) Jo[i] = Joc[0][i] + sg2 * Joc[t][i];
+      emit_row<T, N>(ws, tp, Mrow, lb, rsq, rsqo, nr + k, Jc[0] + sg2 * Jc[t], Jo, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr, -1);
+    }
+    nr += 4;
+  }
+  // whitened smooth force as row nr
+  ws.W[nr][lane] = tp.act ? wsm : T(0);
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < 6; k++) ws.W[nr][32 + k] = tauo[k] * rsqo[k];
+    ws.ax.ncon = ncon; ws.ax.nrow = nr;
+  }
+  __syncwarp();
+
+  // ------------------------------------------------------------------ A = W W^T (+ column W . w_s)
+  // lane owns rows r0 = lane and r1 = lane + 32
+  const int r0 = lane, r1 = lane + 32;
+#pragma unroll 1
+  for (int slot = 0; slot < 2; slot++) {
+    int r = slot ? r1 : r0;
+    if (slot == 1 && nr <= 32) break;
+    bool own = r < nr;
+    T wr[38];
+#pragma unroll
+    for (int k = 0; k < 38; k++) wr[k] = own ? ws.W[r][k] : T(0);
+    for (int cc = 0; cc <= nr; cc++) {
+      T acc = 0;
+#pragma unroll
+      for (int k = 0; k < 38; k++) acc += wr[k] * ws.W[cc][k];
+      if (own) ws.A[r][cc] = acc;
+    }
+  }
+  __syncwarp();
+  // regulariser, reference acceleration, PGS state per owned row
+  T pf[2], py[2], pb[2], pR[2], pinv[2]; int ptype[2];
+  {
+    T tc = maxT<T>(M.solref_tc, 2 * dt), dr = M.solref_dr, dmax = M.solimp[1];
+    T kk = T(1) / (dmax * dmax * tc * tc * dr * dr), bb = T(2) / (dmax * tc);
+#pragma unroll
+    for (int slot = 0; slot < 2; slot++) {
+      int r = slot ? r1 : r0;
+      pf[slot] = 0; py[slot] = 0; pb[slot] = 0; pR[slot] = 1; pinv[slot] = 0; ptype[slot] = ROW_EQ;
+      if (r < nr) {
+        T pos = ws.rpos[r];
+        T imp = impedance<T>(M.solimp, pos);
+        T aref = -bb * ws.rjv[r] - kk * imp * pos;
+        int type = ws.rtype[r];
+        T Arr = ws.A[r][r], Rv;
+        if (type == ROW_CONTACT) {
+          int rf = ws.rfirst[r]; T mu = ws.rmu[r];
+          T Ann = T(0.25) * (ws.A[rf][rf] + ws.A[rf + 1][rf + 1] + 2 * ws.A[rf][rf + 1]);
+          Rv = 2 * mu * mu * (1 - imp) / imp * (1 + mu * mu) * Ann;
+        } else Rv = (1 - imp) / imp * Arr;
+        Rv = maxT<T>(Rv, T(1e-15));
+        pR[slot] = Rv; pinv[slot] = T(1) / (Arr + Rv); pb[slot] = ws.A[r][nr] - aref; ptype[slot] = type;
+        pf[slot] = (e.nrow_prev == nr) ? e.fprev[r] : T(0);
+      }
+    }
+  }
+  __syncwarp();
+  // y = A f for the warm start
+  if (e.nrow_prev == nr) {
+    for (int cc = 0; cc < nr; cc++) {
+      T fc = e.fprev[cc];
+      if (r0 < nr) py[0] += ws.A[r0][cc] * fc;
+      if (r1 < nr) py[1] += ws.A[r1][cc] * fc;
+    }
+  }
+  // ------------------------------------------------------------------ dual projected Gauss-Seidel
+  int iters = 0;
+  {
+    const int maxit = sizeof(T) == 8 ? 4000 : 200;
+    const T tol = sizeof(T) == 8 ? T(1e-13) : T(2e-7);
+    for (; iters < maxit && nr > 0;) {
+      T change = 0, scale = 0;
+      for (int r = 0; r < nr; r++) {
+        const int owner = r & 31;
+        T delta, fnew;
+        if (r < 32) {
+          fnew = pf[0] - (pb[0] + pR[0] * pf[0] + py[0]) * pinv[0];
+          if (ptype[0] != ROW_EQ && fnew < 0) fnew = 0;
+          delta = fnew - pf[0];
+          if (lane == owner) pf[0] = fnew;
+        } else {
+          fnew = pf[1] - (pb[1] + pR[1] * pf[1] + py[1]) * pinv[1];
+          if (ptype[1] != ROW_EQ && fnew < 0) fnew = 0;
+          delta = fnew - pf[1];
+          if (lane == owner) pf[1] = fnew;
+        }
+        delta = __shfl_sync(GMJ_FULL, delta, owner);
+        fnew = __shfl_sync(GMJ_FULL, fnew, owner);
+        if (r0 < nr) py[0] += ws.A[r0][r] * delta;
+        if (r1 < nr) py[1] += ws.A[r1][r] * delta;
+        change = maxT<T>(change, absT<T>(delta)); scale = maxT<T>(scale, absT<T>(fnew));
+      }
+      iters++;
+      if (change <= tol * (1 + scale)) break;
+    }
+  }
+  if (r0 < nr) e.fprev[r0] = pf[0];
+  if (r1 < nr) e.fprev[r1] = pf[1];
+  if (lane == 0) { e.nrow_prev = nr; ws.ax.niter = iters; }
+  __syncwarp();
+
+  // ------------------------------------------------------------------ constraint force, integration
+  T g = 0, go = 0;
+  for (int r = 0; r < nr; r++) {
+    T fr = e.fprev[r];
+    g += ws.W[r][lane] * fr;
+    if (lane < 6) go += ws.W[r][32 + lane] * fr;
+  }
+  // tau_c = L D^1/2 g
+  T tauc = ldl_mulL<T, N>(tp, Mrow, lb, tp.act ? g * sqrtT<T>(D) : T(0));
+  // limit-row forces acting on the base joint enter the wrist force sensor
+  if (lane == 0) {
+    for (int r = 0; r < nr; r++) if (ws.rtype[r] == ROW_LIMIT && ws.rlane[r] == 0) wrist += ws.rmu[r] * e.fprev[r];
+    ws.ax.wrist_z = wrist;
+  }
+  // contact forces in the contact frame (mj_contactForce, pyramidal condim 3)
+  if (lane < ncon) {
+    DevContact<T>& cn = ws.ax.con[lane];
+    int rr = cn.row;
+    T f0 = e.fprev[rr], f1 = e.fprev[rr + 1], f2 = e.fprev[rr + 2], f3 = e.fprev[rr + 3];
+    cn.force[0] = f0 + f1 + f2 + f3; cn.force[1] = cn.mu * (f0 - f1); cn.force[2] = cn.mu * (f2 - f3);
+  }
+  // Euler with implicit damping: (M + h D) a = tau + tau_c
+  T x = ldl_fwd<T, N>(tp, M2row, lb2, tau + tauc);
+  x = tp.act ? x / D2 : T(0);
+  {
+    T xb = __shfl_sync(GMJ_FULL, x, 0);
+    if (lane != 0 && tp.act) x -= lb2 * xb;
+    int fi = tp.chain ? (lane - 1) / NL : 0;
+#pragma unroll
+    for (int k = NL - 1; k >= 1; k--) {
+      T xk = __shfl_sync(GMJ_FULL, x, tp.fb + k);
+      if (tp.chain && tp.local < k) x -= ws.L2[fi][k][tp.local] * xk;
+    }
+  }
+  bad |= !(absT<T>(x) < T(1e10));
+  bad |= !(D2 > 0) && tp.act;
+  if (tp.act) { qd += dt * x; q += dt * qd; e.qpos[lane] = q; e.qvel[lane] = qd; }
+  // object
+  if (has_obj) {
+    T ao[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) { T gk = __shfl_sync(GMJ_FULL, go, k); ao[k] = (tauo[k] + gk / rsqo[k]) / Mo[k]; bad |= !(absT<T>(ao[k]) < T(1e10)); }
+    if (lane == 0) {
+      vo = vo + mk<T>(ao[0], ao[1], ao[2]) * dt; wo = wo + mk<T>(ao[3], ao[4], ao[5]) * dt;
+      e.qvel[32] = vo.x; e.qvel[33] = vo.y; e.qvel[34] = vo.z; e.qvel[35] = wo.x; e.qvel[36] = wo.y; e.qvel[37] = wo.z;
+      e.qpos[32] += dt * vo.x; e.qpos[33] += dt * vo.y; e.qpos[34] += dt * vo.z;
+      T ang = sqrtT<T>(dot(wo, wo)) * dt;
+      T a0 = e.qpos[35], a1 = e.qpos[36], a2 = e.qpos[37], a3 = e.qpos[38];
+      if (ang > 0) {
+        V3<T> axn = normalized(wo);
+        T s, cs; sincosT<T>(ang / 2, &s, &cs);
+        T d0 = cs, d1 = axn.x * s, d2 = axn.y * s, d3 = axn.z * s;
+        T n0 = a0 * d0 - a1 * d1 - a2 * d2 - a3 * d3, n1 = a0 * d1 + a1 * d0 + a2 * d3 - a3 * d2;
+        T n2 = a0 * d2 - a1 * d3 + a2 * d0 + a3 * d1, n3 = a0 * d3 + a1 * d2 - a2 * d1 + a3 * d0;
+        a0 = n0; a1 = n1; a2 = n2; a3 = n3;
+      }
+      T l = T(1) / sqrtT<T>(a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3);
+      e.qpos[35] = a0 * l; e.qpos[36] = a1 * l; e.qpos[37] = a2 * l; e.qpos[38] = a3 * l;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 6; k++) (void)__shfl_sync(GMJ_FULL, go, k);
+  }
+  unsigned anybad = __ballot_sync(GMJ_FULL, bad);
+  if (lane == 0) {
+    if (anybad) e.unstable = 1;
+    e.time += dtd;
+    e.st_substeps++; e.st_contacts += ncon; e.st_rows += nr; e.st_iters += iters;
+  }
+  __syncwarp();
+}

@@ -1,0 +1,88 @@
+/* gmj.h -- C ABI of libgripper_b200.so: the batched, B200-resident replacement for the
+ * hot path of the reference's pybind module (rl/env/mjpy/bind.so, class MjClass, src/bind.cpp).
+ *
+ * Every entry point returns 0 on success, non-zero on error (gmj_last_error() gives the text).
+ * All pointers named *_dev are DEVICE pointers on the handle's GPU, all pointers named *_host are
+ * host pointers; the library owns every piece of simulation state, the caller owns in/out buffers.
+ * No entry point synchronises the host except gmj_*_host() and gmj_stats().
+ *
+ * Reference interface each entry replaces (path:line in lukebeddow/gripper-mujoco):
+ *   gmj_create / gmj_destroy     MjClass::MjClass / load / init        src/mjclass.cpp:22-79,377-409 ; src/bind.cpp:43-52
+ *   gmj_set_settings             MjClass::set (mj.set.<field> r/w)      src/bind.cpp:195-204,246-365
+ *   gmj_set_objects              luke::get_objects / ObjectHandler::init src/objecthandler.cpp:22-133
+ *   gmj_reset                    MjClass::reset                         src/mjclass.cpp:434-486 ; src/bind.cpp:55
+ *   gmj_spawn                    MjClass::spawn_object(idx,x,y,rot)     src/mjclass.cpp:2323-2420 ; src/bind.cpp:88-95
+ *   gmj_step                     set_action + action_step + get_observation + reward + is_done
+ *                                src/mjclass.cpp:1483-1698,1700-1959,3000-3049 ; src/bind.cpp:60-66,119-123
+ *   gmj_set_action               MjClass::set_action                    src/mjclass.cpp:1528-1630
+ *   gmj_action_step              MjClass::action_step                   src/mjclass.cpp:1483-1508
+ *   gmj_substeps                 MjClass::step (n times)                src/mjclass.cpp:504-530 ; src/bind.cpp:57
+ *   gmj_observe                  get_observation / reward / is_done / get_event_state
+ *   gmj_get_state                data->qpos / qvel reads (parity dumps)
+ *   gmj_probe                    read_armadillo_gauge / sim_sensors_SI_ latest / calibrate_reset
+ *   gmj_stats                    (new) solver + stability counters, mirrors BADQACC src/myfunctions.cpp:4233
+ */
+#ifndef GMJ_H_
+#define GMJ_H_
+
+#include <stdint.h>
+#include "gmj_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct GmjHandle GmjHandle;
+
+/* precision: 0 = FP32 physics (product), 1 = FP64 physics (validation build of the same kernels) */
+int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, int device,
+               int precision, uint32_t env_id_offset, GmjHandle** out);
+int gmj_destroy(GmjHandle* h);
+int gmj_set_settings(GmjHandle* h, const GmjSettings* settings);
+int gmj_set_objects(GmjHandle* h, const GmjObject* objects_host, int n_objects);
+
+/* mask_dev: uint8[n_envs] (NULL = all). episode_dev: uint32[n_envs] episode counters or NULL
+ * (NULL = per-env counter kept by the library). stream: cudaStream_t as void*. */
+int gmj_reset(GmjHandle* h, const uint8_t* mask_dev, void* stream);
+/* idx_dev int32[n_envs], xyr_dev float[n_envs][3] (x, y, z-rotation); idx_dev == NULL draws object,
+ * position (2 mm grid within +-xy_range) and rotation (pi/30 grid within +-rot_range) per env from the
+ * counter-based RNG, rejecting poses that overlap the fingertip boxes (spawn_into_scene,
+ * src/mjclass.cpp:2475-2654). mask_dev as above. */
+int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const uint8_t* mask_dev,
+              float xy_range, float rot_range, void* stream);
+
+/* fused hot path: actions_dev int32[n_envs] (discrete action index), frac_dev float[n_envs] or NULL.
+ * Outputs (any may be NULL): obs_dev float[n_envs][n_obs], reward_dev float[n_envs],
+ * done_dev uint8[n_envs], events_dev float[n_envs][57]. */
+int gmj_step(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, float* obs_dev,
+             float* reward_dev, uint8_t* done_dev, float* events_dev, void* stream);
+int gmj_set_action(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, void* stream);
+int gmj_action_step(GmjHandle* h, void* stream);
+int gmj_substeps(GmjHandle* h, int n, int sensors, void* stream);
+/* observation / reward (side effect on the cumulative reward exactly like MjClass::reward, call once
+ * per step) / done / event vector of the CURRENT state without stepping */
+int gmj_observe(GmjHandle* h, float* obs_dev, float* reward_dev, uint8_t* done_dev, float* events_dev,
+                void* stream);
+
+int gmj_n_obs(GmjHandle* h);
+int gmj_n_actions(GmjHandle* h);
+int gmj_n_envs(GmjHandle* h);
+/* copies qpos[n_envs][nq] / qvel[n_envs][nv] (reference joint order, double) to host buffers */
+int gmj_get_state_host(GmjHandle* h, double* qpos_host, double* qvel_host);
+/* per-env probe, double[n_envs][GMJ_PROBE_LEN] to host: see enum below */
+enum { GP_time = 0, GP_wrist_z, GP_gauge0, GP_gauge1, GP_gauge2, GP_si_gauge0, GP_si_gauge1, GP_si_gauge2,
+       GP_si_palm, GP_si_wrist, GP_ncon, GP_nrow, GP_niter, GP_unstable, GP_weld_on, GP_base_z,
+       GP_tend_x, GP_tend_y, GP_tend_z, GP_tend_th, GP_tnext_x, GP_tnext_y, GP_tnext_z, GP_tnext_th,
+       GP_cumulative_reward, GP_has_object, GP_obj_index, GP_episode, GP_last_reward, GP_last_done,
+       GMJ_PROBE_LEN = 32 };
+int gmj_probe_host(GmjHandle* h, double* probe_host);
+int gmj_stats(GmjHandle* h, GmjStats* out);
+/* overwrite joint positions of all envs with qpos (host, double[nq]) and zero velocities: used by the
+ * calibration flow (calibrate_reset writes qpos directly, src/myfunctions.cpp:1497-1516) */
+int gmj_set_welds(GmjHandle* h, int mask_on, void* stream);
+const char* gmj_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -158,7 +158,9 @@ enum { GSM_raw = 0, GSM_change, GSM_average, GSM_median, GSM_sign, GSM_scaled_ch
 
 #define GMJ_EVENT_STATE_LEN 57   /* 15 + 2*21, src/mjclass.cpp:5594-5615 */
 #define GMJ_MAX_OBS 160          /* 19+ streams * (2*prev_steps+1) upper bound */
-#define GMJ_MAXCON 12            /* contacts kept per env per substep */
+#define GMJ_MAXROW 48           /* constraint rows kept per env per substep; a contact whose 4 rows
+                                    do not fit is dropped together with all later contacts */
+#define GMJ_MAXCON 10            /* contacts kept per env per substep */
 
 /* per-env parity dump (qpos/qvel in reference order, sensors, contact stats) */
 typedef struct GmjStateView {

@@ -163,7 +163,11 @@ float or_read_gauge(const OrEnv* e, int finger) {
     coeff[k] = (X[k][k] != 0) ? s / X[k][k] : 0;
   }
   float yv = 0.0f;
-  for (int i = 0; i <= 3; i++) yv = (float)(yv + coeff[i] * pow(50e-3, 3 - i));
+  const double xp = 50e-3;   /* std::pow(xpos, order - i), written as products (same on the device path) */
+  yv = (float)(yv + coeff[0] * (xp * xp * xp));
+  yv = (float)(yv + coeff[1] * (xp * xp));
+  yv = (float)(yv + coeff[2] * xp);
+  yv = (float)(yv + coeff[3] * 1.0);
   return yv * 1000;
 }
 
@@ -512,7 +516,7 @@ static void sense_gripper_state(OrEnv* e) {
   for (int i = 0; i < 3; i++) {
     double ang = i * PI_23;
     double tilt_x = fing_x - L * sin(fing_th);
-    double defl = F[i] * pow(L, 3) / (3 * e->m.EI);
+    double defl = F[i] * (L * L * L) / (3 * e->m.EI);
     double fx = tilt_x + defl * cos(fing_th);
     double px = -fx * sin(ang + e->base_yaw) + e->base_x;
     double py = -fx * cos(ang + e->base_yaw) + e->base_y;

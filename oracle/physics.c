@@ -279,12 +279,13 @@ void or_physics_step(OrEnv* e) {
   /* joint limits (margin 0) */
   for (int i = 0; i < B; i++) {
     double lo = e->qpos[i] - m->range_lo[i], hi = m->range_hi[i] - e->qpos[i];
-    if (lo < 0) { memset(J[nr], 0, sizeof(double) * nv); J[nr][i] = 1; rpos[nr] = lo; rtype[nr++] = ROW_LIMIT; }
-    if (hi < 0) { memset(J[nr], 0, sizeof(double) * nv); J[nr][i] = -1; rpos[nr] = hi; rtype[nr++] = ROW_LIMIT; }
+    if (lo < 0 && nr < GMJ_MAXROW) { memset(J[nr], 0, sizeof(double) * nv); J[nr][i] = 1; rpos[nr] = lo; rtype[nr++] = ROW_LIMIT; }
+    if (hi < 0 && nr < GMJ_MAXROW) { memset(J[nr], 0, sizeof(double) * nv); J[nr][i] = -1; rpos[nr] = hi; rtype[nr++] = ROW_LIMIT; }
   }
   /* contacts: pyramidal cone, condim 3 -> 4 rows (n + mu t1, n - mu t1, n + mu t2, n - mu t2) */
   for (int c = 0; c < e->ncon; c++) {
     OrContact* cn = &e->con[c];
+    if (nr + 4 > GMJ_MAXROW) { e->ncon = c; break; }   /* row cap shared with the device path */
     cn->row = nr;
     jac_point(e, cn->body1, cn->pos, Jp1, Jr1);
     jac_point(e, cn->body2, cn->pos, Jp2, Jr2);

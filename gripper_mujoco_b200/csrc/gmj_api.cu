@@ -397,3 +397,219 @@ static int build_settings(const GmjSettings* s, DevSettings* d) {
   d->n_obs = no;
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------ C ABI
+template <typename T, int N>
+static int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
+                          float* reward, uint8_t* done, float* events, cudaStream_t st) {
+  size_t smem = sizeof(WarpShared<T, N>) * WARPS_PER_BLOCK;
+  static bool attr_set = false;
+  if (!attr_set) { CK(cudaFuncSetAttribute(k_step<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
+  int blocks = (h->n_envs + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
+  k_step<T, N><<<blocks, 32 * WARPS_PER_BLOCK, smem, st>>>((EnvState<T>*)h->envs, (const DevModel<T>*)h->model, h->settings,
+      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag);
+  CK(cudaGetLastError());
+  h->smem_bytes = smem;
+  return 0;
+}
+template <typename T>
+static int launch_step_T(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
+                         float* reward, uint8_t* done, float* events, cudaStream_t st) {
+  switch (h->N) {
+    case 5: return launch_step_TN<T, 5>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
+    case 8: return launch_step_TN<T, 8>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
+    default: FAIL("this build instantiates the step kernel for N = 5 and N = 8 segments only");
+  }
+}
+static int launch_step(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
+                       float* reward, uint8_t* done, float* events, void* stream) {
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (h->precision == 0) return launch_step_T<float>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
+  return launch_step_T<double>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
+}
+static size_t env_bytes(const GmjHandle* h) { return h->precision == 0 ? sizeof(EnvState<float>) : sizeof(EnvState<double>); }
+
+extern "C" {
+
+const char* gmj_last_error(void) { return g_err.c_str(); }
+
+int gmj_set_settings(GmjHandle* h, const GmjSettings* settings) {
+  if (!h || !settings) FAIL("null argument");
+  CK(cudaSetDevice(h->device));
+  if (build_settings(settings, &h->hs)) return 1;
+  CK(cudaMemcpy(h->settings, &h->hs, sizeof(DevSettings), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, int device, int precision,
+               uint32_t env_id_offset, GmjHandle** out) {
+  if (!model || !settings || !out || n_envs <= 0) FAIL("bad argument to gmj_create");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) FAIL("no CUDA device: libgripper_b200 has no CPU fallback");
+  CK(cudaSetDevice(device));
+  GmjHandle* h = new GmjHandle();
+  memset(h, 0, sizeof(*h));
+  h->n_envs = n_envs; h->device = device; h->precision = precision; h->N = model->N; h->B = model->B; h->hm = *model;
+  h->env_id_offset = env_id_offset;
+  if (precision == 0) {
+    DevModel<float> dm; if (build_model<float>(model, &dm)) { delete h; return 1; }
+    CK(cudaMalloc(&h->model, sizeof(dm))); CK(cudaMemcpy(h->model, &dm, sizeof(dm), cudaMemcpyHostToDevice));
+  } else {
+    DevModel<double> dm; if (build_model<double>(model, &dm)) { delete h; return 1; }
+    CK(cudaMalloc(&h->model, sizeof(dm))); CK(cudaMemcpy(h->model, &dm, sizeof(dm), cudaMemcpyHostToDevice));
+  }
+  CK(cudaMalloc(&h->envs, env_bytes(h) * (size_t)n_envs));
+  CK(cudaMemset(h->envs, 0, env_bytes(h) * (size_t)n_envs));
+  CK(cudaMalloc(&h->settings, sizeof(DevSettings)));
+  CK(cudaMalloc(&h->err_flag, sizeof(int))); CK(cudaMemset(h->err_flag, 0, sizeof(int)));
+  CK(cudaMalloc(&h->stats_dev, 8 * sizeof(unsigned long long)));
+  if (gmj_set_settings(h, settings)) { return 1; }
+  *out = h;
+  return gmj_reset(h, nullptr, nullptr);
+}
+
+int gmj_destroy(GmjHandle* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaFree(h->envs); cudaFree(h->model); cudaFree(h->settings); cudaFree(h->err_flag); cudaFree(h->stats_dev);
+  if (h->objects) cudaFree(h->objects);
+  if (h->scratch) cudaFree(h->scratch);
+  delete h;
+  return 0;
+}
+
+int gmj_set_objects(GmjHandle* h, const GmjObject* objects_host, int n_objects) {
+  if (!h || !objects_host || n_objects <= 0) FAIL("bad argument to gmj_set_objects");
+  CK(cudaSetDevice(h->device));
+  if (h->objects) CK(cudaFree(h->objects));
+  CK(cudaMalloc(&h->objects, sizeof(GmjObject) * (size_t)n_objects));
+  CK(cudaMemcpy(h->objects, objects_host, sizeof(GmjObject) * (size_t)n_objects, cudaMemcpyHostToDevice));
+  h->n_objects = n_objects;
+  return 0;
+}
+
+int gmj_reset(GmjHandle* h, const uint8_t* mask_dev, void* stream) {
+  if (!h) FAIL("null handle");
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  int tb = 128, nb = (h->n_envs + tb - 1) / tb;
+  if (h->precision == 0) k_reset<float><<<nb, tb, 0, st>>>((EnvState<float>*)h->envs, (const DevModel<float>*)h->model, h->settings, h->n_envs, mask_dev, h->env_id_offset);
+  else k_reset<double><<<nb, tb, 0, st>>>((EnvState<double>*)h->envs, (const DevModel<double>*)h->model, h->settings, h->n_envs, mask_dev, h->env_id_offset);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const uint8_t* mask_dev, float xy_range,
+              float rot_range, void* stream) {
+  if (!h) FAIL("null handle");
+  if (!h->objects) FAIL("gmj_spawn before gmj_set_objects");
+  if (idx_dev && !xyr_dev) FAIL("gmj_spawn: idx_dev given without xyr_dev");
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  int tb = 128, nb = (h->n_envs + tb - 1) / tb;
+  if (h->precision == 0) k_spawn<float><<<nb, tb, 0, st>>>((EnvState<float>*)h->envs, (const DevModel<float>*)h->model, h->settings, h->objects, h->n_objects, h->n_envs, idx_dev, xyr_dev, mask_dev, xy_range, rot_range, h->err_flag);
+  else k_spawn<double><<<nb, tb, 0, st>>>((EnvState<double>*)h->envs, (const DevModel<double>*)h->model, h->settings, h->objects, h->n_objects, h->n_envs, idx_dev, xyr_dev, mask_dev, xy_range, rot_range, h->err_flag);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int gmj_step(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, float* obs_dev, float* reward_dev,
+             uint8_t* done_dev, float* events_dev, void* stream) {
+  if (!h || !actions_dev) FAIL("gmj_step: null handle or actions");
+  return launch_step(h, STEP_SET_ACTION | STEP_SUBSTEPS | STEP_SENSORS | STEP_TAIL | STEP_OUTPUT, -1, actions_dev, frac_dev,
+                     obs_dev, reward_dev, done_dev, events_dev, stream);
+}
+int gmj_set_action(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, void* stream) {
+  if (!h || !actions_dev) FAIL("gmj_set_action: null handle or actions");
+  // the termination action burns 2 x sim_steps_per_action substeps inside set_action (quirk Q8)
+  return launch_step(h, STEP_SET_ACTION | STEP_SUBSTEPS | STEP_SENSORS, 0, actions_dev, frac_dev, nullptr, nullptr, nullptr, nullptr, stream);
+}
+int gmj_action_step(GmjHandle* h, void* stream) {
+  if (!h) FAIL("null handle");
+  return launch_step(h, STEP_SUBSTEPS | STEP_SENSORS | STEP_TAIL, -1, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, stream);
+}
+int gmj_substeps(GmjHandle* h, int n, int sensors, void* stream) {
+  if (!h || n < 0) FAIL("bad argument to gmj_substeps");
+  return launch_step(h, STEP_SUBSTEPS | (sensors ? STEP_SENSORS : 0), n, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, stream);
+}
+int gmj_observe(GmjHandle* h, float* obs_dev, float* reward_dev, uint8_t* done_dev, float* events_dev, void* stream) {
+  if (!h) FAIL("null handle");
+  return launch_step(h, STEP_OUTPUT, 0, nullptr, nullptr, obs_dev, reward_dev, done_dev, events_dev, stream);
+}
+
+int gmj_n_obs(GmjHandle* h) { return h ? h->hs.n_obs : -1; }
+int gmj_n_actions(GmjHandle* h) { return h ? h->hs.n_actions : -1; }
+int gmj_n_envs(GmjHandle* h) { return h ? h->n_envs : -1; }
+
+static int ensure_scratch(GmjHandle* h, size_t n) {
+  if (h->scratch_len >= n) return 0;
+  if (h->scratch) CK(cudaFree(h->scratch));
+  CK(cudaMalloc(&h->scratch, n * sizeof(double)));
+  h->scratch_len = n;
+  return 0;
+}
+
+int gmj_get_state_host(GmjHandle* h, double* qpos_host, double* qvel_host) {
+  if (!h) FAIL("null handle");
+  CK(cudaSetDevice(h->device));
+  size_t nq = (size_t)h->n_envs * (h->B + 7), nv = (size_t)h->n_envs * (h->B + 6);
+  if (ensure_scratch(h, nq + nv)) return 1;
+  int tb = 128, nb = (h->n_envs + tb - 1) / tb;
+  if (h->precision == 0) k_dump<float><<<nb, tb>>>((const EnvState<float>*)h->envs, h->n_envs, h->B, h->scratch, h->scratch + nq, nullptr);
+  else k_dump<double><<<nb, tb>>>((const EnvState<double>*)h->envs, h->n_envs, h->B, h->scratch, h->scratch + nq, nullptr);
+  CK(cudaGetLastError());
+  if (qpos_host) CK(cudaMemcpy(qpos_host, h->scratch, nq * sizeof(double), cudaMemcpyDeviceToHost));
+  if (qvel_host) CK(cudaMemcpy(qvel_host, h->scratch + nq, nv * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int gmj_probe_host(GmjHandle* h, double* probe_host) {
+  if (!h || !probe_host) FAIL("null argument");
+  CK(cudaSetDevice(h->device));
+  size_t n = (size_t)h->n_envs * GMJ_PROBE_LEN;
+  if (ensure_scratch(h, n)) return 1;
+  int tb = 128, nb = (h->n_envs + tb - 1) / tb;
+  if (h->precision == 0) {
+    k_dump<float><<<nb, tb>>>((const EnvState<float>*)h->envs, h->n_envs, h->B, nullptr, nullptr, h->scratch);
+    if (h->N == 5) k_gauge<float, 5><<<nb, tb>>>((const EnvState<float>*)h->envs, (const DevModel<float>*)h->model, h->n_envs, h->scratch);
+    else if (h->N == 8) k_gauge<float, 8><<<nb, tb>>>((const EnvState<float>*)h->envs, (const DevModel<float>*)h->model, h->n_envs, h->scratch);
+  } else {
+    k_dump<double><<<nb, tb>>>((const EnvState<double>*)h->envs, h->n_envs, h->B, nullptr, nullptr, h->scratch);
+    if (h->N == 5) k_gauge<double, 5><<<nb, tb>>>((const EnvState<double>*)h->envs, (const DevModel<double>*)h->model, h->n_envs, h->scratch);
+    else if (h->N == 8) k_gauge<double, 8><<<nb, tb>>>((const EnvState<double>*)h->envs, (const DevModel<double>*)h->model, h->n_envs, h->scratch);
+  }
+  CK(cudaGetLastError());
+  CK(cudaMemcpy(probe_host, h->scratch, n * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int gmj_stats(GmjHandle* h, GmjStats* out) {
+  if (!h || !out) FAIL("null argument");
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemset(h->stats_dev, 0, 8 * sizeof(unsigned long long)));
+  int tb = 128, nb = (h->n_envs + tb - 1) / tb;
+  if (h->precision == 0) k_stats<float><<<nb, tb>>>((const EnvState<float>*)h->envs, h->n_envs, h->stats_dev);
+  else k_stats<double><<<nb, tb>>>((const EnvState<double>*)h->envs, h->n_envs, h->stats_dev);
+  CK(cudaGetLastError());
+  unsigned long long v[8];
+  CK(cudaMemcpy(v, h->stats_dev, sizeof(v), cudaMemcpyDeviceToHost));
+  out->substeps = (int64_t)v[0]; out->unstable_resets = (int64_t)v[1]; out->contacts = (int64_t)v[2];
+  out->rows = (int64_t)v[3]; out->solver_iters = (int64_t)v[4]; out->contact_overflow = (int64_t)v[5];
+  int ef = 0;
+  CK(cudaMemcpy(&ef, h->err_flag, sizeof(int), cudaMemcpyDeviceToHost));
+  if (ef) { CK(cudaMemset(h->err_flag, 0, sizeof(int))); g_err = ef == 1 ? "an action index was out of range" : "a spawn object index was out of range"; return 2; }
+  return 0;
+}
+
+int gmj_set_welds(GmjHandle* h, int mask_on, void* stream) {
+  if (!h) FAIL("null handle");
+  CK(cudaSetDevice(h->device));
+  int tb = 128, nb = (h->n_envs + tb - 1) / tb;
+  if (h->precision == 0) k_set_welds<float><<<nb, tb, 0, (cudaStream_t)stream>>>((EnvState<float>*)h->envs, h->n_envs, h->B, h->N, mask_on);
+  else k_set_welds<double><<<nb, tb, 0, (cudaStream_t)stream>>>((EnvState<double>*)h->envs, h->n_envs, h->B, h->N, mask_on);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

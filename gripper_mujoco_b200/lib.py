@@ -1,0 +1,101 @@
+"""ctypes loader of libgripper_b200.so (include/gmj.h). There is NO CPU fallback: if the library is
+missing or cannot be loaded this module raises, and gmj_create itself fails without a CUDA device.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+from .model import GmjModel, GmjObject
+from .settings import GmjSettings
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libgripper_b200.so")
+CSRC = os.path.join(_HERE, "csrc")
+SOURCES = ["gmj_api.cu", "gmj_physics.cuh", "gmj_tail.cuh", "gmj_collide.cuh", "gmj_device.cuh"]
+HEADERS = [os.path.join(_HERE, "..", "include", h) for h in ("gmj.h", "gmj_types.h")]
+
+GMJ_PROBE_LEN = 32
+GMJ_EVENT_STATE_LEN = 57
+PROBE_FIELDS = ["time", "wrist_z", "gauge0", "gauge1", "gauge2", "si_gauge0", "si_gauge1", "si_gauge2",
+                "si_palm", "si_wrist", "ncon", "nrow", "niter", "unstable", "weld_on", "base_z",
+                "tend_x", "tend_y", "tend_z", "tend_th", "tnext_x", "tnext_y", "tnext_z", "tnext_th",
+                "cumulative_reward", "has_object", "obj_index", "episode", "last_reward", "last_done"]
+GP = {n: i for i, n in enumerate(PROBE_FIELDS)}
+
+# every symbol include/gmj.h declares (tests check the .so exports exactly these)
+SYMBOLS = ["gmj_create", "gmj_destroy", "gmj_set_settings", "gmj_set_objects", "gmj_reset", "gmj_spawn",
+           "gmj_step", "gmj_set_action", "gmj_action_step", "gmj_substeps", "gmj_observe", "gmj_n_obs",
+           "gmj_n_actions", "gmj_n_envs", "gmj_get_state_host", "gmj_probe_host", "gmj_stats",
+           "gmj_set_welds", "gmj_last_error"]
+
+
+class GmjStats(C.Structure):
+    _fields_ = [("substeps", C.c_int64), ("unstable_resets", C.c_int64), ("contacts", C.c_int64),
+                ("rows", C.c_int64), ("solver_iters", C.c_int64), ("contact_overflow", C.c_int64)]
+
+
+def nvcc_command(out: str = SO_PATH, extra: list[str] | None = None) -> list[str]:
+    return ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+            "-shared", "-Xcompiler", "-fPIC", *(extra or []), "-o", out, os.path.join(CSRC, "gmj_api.cu")]
+
+
+def stale() -> bool:
+    if not os.path.exists(SO_PATH):
+        return True
+    t = os.path.getmtime(SO_PATH)
+    deps = [os.path.join(CSRC, s) for s in SOURCES] + HEADERS
+    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile the CUDA extension for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
+    if force or stale():
+        cmd = nvcc_command(extra=["-Xptxas", "-v"] if verbose else None)
+        subprocess.check_call(cmd)
+    return SO_PATH
+
+
+_LIB = None
+
+
+def lib():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(SO_PATH):
+        raise RuntimeError(
+            f"{SO_PATH} is missing: the CUDA extension is the only implementation of the hot path "
+            "(no CPU fallback). Build it with `python -c 'import __graft_entry__ as g; g.build()'`.")
+    L = C.CDLL(SO_PATH)
+    vp, i32, f32 = C.c_void_p, C.c_int, C.c_float
+    L.gmj_last_error.restype = C.c_char_p
+    L.gmj_create.argtypes = [C.POINTER(GmjModel), C.POINTER(GmjSettings), i32, i32, i32, C.c_uint32, C.POINTER(vp)]
+    L.gmj_destroy.argtypes = [vp]
+    L.gmj_set_settings.argtypes = [vp, C.POINTER(GmjSettings)]
+    L.gmj_set_objects.argtypes = [vp, C.POINTER(GmjObject), i32]
+    L.gmj_reset.argtypes = [vp, vp, vp]
+    L.gmj_spawn.argtypes = [vp, vp, vp, vp, f32, f32, vp]
+    L.gmj_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
+    L.gmj_set_action.argtypes = [vp, vp, vp, vp]
+    L.gmj_action_step.argtypes = [vp, vp]
+    L.gmj_substeps.argtypes = [vp, i32, i32, vp]
+    L.gmj_observe.argtypes = [vp, vp, vp, vp, vp, vp]
+    for f in ("gmj_n_obs", "gmj_n_actions", "gmj_n_envs"):
+        getattr(L, f).argtypes = [vp]
+    L.gmj_get_state_host.argtypes = [vp, vp, vp]
+    L.gmj_probe_host.argtypes = [vp, vp]
+    L.gmj_stats.argtypes = [vp, C.POINTER(GmjStats)]
+    L.gmj_set_welds.argtypes = [vp, i32, vp]
+    _LIB = L
+    return L
+
+
+class GmjError(RuntimeError):
+    pass
+
+
+def check(rc: int):
+    if rc != 0:
+        raise GmjError(lib().gmj_last_error().decode())

@@ -1,0 +1,110 @@
+"""Shared helpers of the test-suite: identical model / settings for the oracle and the CUDA path."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from gripper_mujoco_b200.model import GripperParams, build_model  # noqa: E402
+from gripper_mujoco_b200.objects import build_object_set  # noqa: E402
+from gripper_mujoco_b200.settings import Settings  # noqa: E402
+from oracle.binding import OracleEnv  # noqa: E402  (tests are allowed to use the oracle)
+
+_CAL_CACHE: dict = {}
+
+
+def oracle_calibration(N: int):
+    """Equilibrium of base + motor joints under gravity with all welds on (calibrate_reset,
+    src/myfunctions.cpp:1497-1516: 400 steps at 2 ms). Computed once per N with the oracle."""
+    if N not in _CAL_CACHE:
+        mdl = build_model(GripperParams(num_segments=N))
+        env = OracleEnv(mdl.to_struct(), Settings().pack())
+        env.settle(400, 2e-3)
+        _CAL_CACHE[N] = np.array(env.peek().reset_qpos[:8])
+    return _CAL_CACHE[N]
+
+
+def make_settings(N: int, timestep: float, steps_per_action: int | None = None, noise: bool = False,
+                  seed: int = 1234) -> Settings:
+    s = Settings()
+    s.mujoco_timestep = timestep
+    s.sim_steps_per_action = steps_per_action or int(np.ceil(s.time_for_action / timestep))
+    s.random_seed = seed
+    rq = oracle_calibration(N)
+    s.reset_qpos_base = float(rq[0])
+    for k in range(7):
+        setattr(s, f"reset_qpos_g{k}", float(rq[1 + k]))
+    s.set_use_noise(noise)
+    s.use_noise_seeded = 1 if noise else 0
+    if not noise:
+        s.base_position_noise = 0.0
+    return s
+
+
+def make_pair(N: int = 5, timestep: float = 2e-3, **kw):
+    mdl = build_model(GripperParams(num_segments=N))
+    st = make_settings(N, timestep, **kw)
+    return mdl, st
+
+
+_OBJ_CACHE = None
+
+
+def objects():
+    global _OBJ_CACHE
+    if _OBJ_CACHE is None:
+        _OBJ_CACHE = build_object_set()
+    return _OBJ_CACHE
+
+
+def find_object(prefix: str):
+    for i, o in enumerate(objects()):
+        if o.name.startswith(prefix):
+            return i, o
+    raise KeyError(prefix)
+
+
+class OracleBatch:
+    """n independent oracle envs driven like GripperBatch (same env ids / episode numbering)."""
+
+    def __init__(self, n, mdl, st, env_id_offset=0):
+        self.ms, self.ss = mdl.to_struct(), st.pack()
+        self.envs = [OracleEnv(self.ms, self.ss) for _ in range(n)]
+        self.episode = 0
+        self.seed = int(st.random_seed)
+        self.off = env_id_offset
+        self.reset()
+
+    def reset(self):
+        self.episode += 1
+        for i, e in enumerate(self.envs):
+            e.reset(self.seed, self.off + i, self.episode)
+
+    def spawn(self, idx, x, y, r):
+        objs = objects()
+        for i, e in enumerate(self.envs):
+            e.spawn(objs[int(np.broadcast_to(idx, (len(self.envs),))[i])].obj,
+                    float(np.broadcast_to(x, (len(self.envs),))[i]),
+                    float(np.broadcast_to(y, (len(self.envs),))[i]),
+                    float(np.broadcast_to(r, (len(self.envs),))[i]))
+
+    def step(self, actions):
+        obs, rew, done, ev = [], [], [], []
+        for e, a in zip(self.envs, actions):
+            rc = e.set_action(int(a))
+            assert rc == 0
+            e.action_step()
+            obs.append(e.observation()); rew.append(e.reward()); done.append(e.is_done()); ev.append(e.event_state())
+        return np.stack(obs), np.array(rew, dtype=np.float32), np.array(done), np.stack(ev)
+
+    def qpos(self):
+        return np.stack([e.qpos() for e in self.envs])
+
+    def qvel(self):
+        return np.stack([e.qvel() for e in self.envs])

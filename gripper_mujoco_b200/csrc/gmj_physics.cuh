@@ -185,6 +185,8 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   constexpr int NL = N + 2, B = 3 * N + 8, PALM = 3 * N + 7;
   const Topo<N> tp(lane);
   EnvState<T>& e = ws.e;
+  // after a BADQACC-class failure the env is frozen until the caller resets it (is_done reports it)
+  if (e.unstable) { __syncwarp(); if (lane == 0) e.time += dtd; __syncwarp(); return; }
   const T gz = -M.zref;                                   // ground plane height in shifted coordinates
 
   // ------------------------------------------------------------------ kinematics

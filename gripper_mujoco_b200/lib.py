@@ -57,6 +57,26 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return SO_PATH
 
 
+FMA_SO = os.path.join(_HERE, "libgmj_fma_peak.so")
+
+
+def build_fma_peak(force: bool = False) -> str:
+    src = os.path.join(CSRC, "fma_peak.cu")
+    if force or not os.path.exists(FMA_SO) or os.path.getmtime(src) > os.path.getmtime(FMA_SO):
+        subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-shared",
+                               "-Xcompiler", "-fPIC", "-o", FMA_SO, src])
+    return FMA_SO
+
+
+def fma_peak_tflops(device: int = 0, iters: int = 20000) -> float:
+    """Measured FP32 FMA-pipe peak of this GPU (TFLOP/s), csrc/fma_peak.cu."""
+    L = C.CDLL(FMA_SO)
+    out = C.c_double()
+    if L.gmj_fma_peak(int(device), int(iters), C.byref(out)) != 0:
+        raise RuntimeError("gmj_fma_peak failed")
+    return out.value
+
+
 _LIB = None
 
 

@@ -211,6 +211,8 @@ void or_physics_step(OrEnv* e) {
   static int rtype[OR_MAXROW];
   static double Jp1[3 * OR_MAXV], Jr1[3 * OR_MAXV], Jp2[3 * OR_MAXV], Jr2[3 * OR_MAXV];
 
+  /* after a BADQACC-class failure the env is frozen until reset (is_done reports it) */
+  if (e->unstable) { e->time += dt; return; }
   /* ---- mj_step1: position + velocity stage */
   or_kinematics(e);
   dynamics(e, M, bias);

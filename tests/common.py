@@ -21,12 +21,15 @@ _CAL_CACHE: dict = {}
 
 def oracle_calibration(N: int):
     """Equilibrium of base + motor joints under gravity with all welds on (calibrate_reset,
-    src/myfunctions.cpp:1497-1516: 400 steps at 2 ms). Computed once per N with the oracle."""
+    src/myfunctions.cpp:1450-1516: 400 steps at 2 ms). Computed once per N with the oracle."""
     if N not in _CAL_CACHE:
-        mdl = build_model(GripperParams(num_segments=N))
-        env = OracleEnv(mdl.to_struct(), Settings().pack())
-        env.settle(400, 2e-3)
-        _CAL_CACHE[N] = np.array(env.peek().reset_qpos[:8])
+        from gripper_mujoco_b200 import calibration
+        from oracle.calibrate import make_backend
+        p = GripperParams(num_segments=N)
+        mdl = build_model(p)
+        s = Settings()
+        calibration.calibrate_reset(p, mdl.N, mdl.B, s, make_backend(mdl))
+        _CAL_CACHE[N] = np.array([s.reset_qpos_base] + [getattr(s, f"reset_qpos_g{k}") for k in range(7)])
     return _CAL_CACHE[N]
 
 

@@ -1,0 +1,230 @@
+"""Parity of the CUDA hot path (through the C ABI, include/gmj.h) against the CPU oracle.
+
+Bars (north_star): event rows / done flags bit-exact over short horizons; qpos, qvel, sensors
+(observation) and reward within the tolerance written beside each test. The FP64 instantiation of
+the same kernels is the tight check of the algorithm; FP32 is the product precision.
+"""
+import numpy as np
+import pytest
+
+from common import OracleBatch, find_object, make_pair, objects
+
+pytestmark = pytest.mark.gpu
+
+DISCRETE = list(range(15)) + [15 + 2 * k for k in range(21)]      # event rows (EventTrack::vectorise)
+CONTINUOUS = [16 + 2 * k for k in range(21)]                       # linear events' last_value
+
+# tolerance per precision: (qpos, qvel, obs, reward, event last_value)
+TOL = {"fp64": (1e-8, 1e-6, 1e-7, 1e-6, 1e-6), "fp32": (5e-3, 1e-1, 2e-2, 1e-3, 5e-2)}
+
+OBJECTS = ["cube_fillet_0_3", "cylinder_12_upright_fillet_0_5", "sphere_", "cuboid_311_thinner_fillet_20_3",
+           "ellipse_1p51_52"]
+
+
+def _batch(n, mdl, st, precision):
+    from gripper_mujoco_b200.batch import GripperBatch
+    gb = GripperBatch(n, mdl, st, precision=precision)
+    gb.set_objects(objects())
+    return gb
+
+
+def _compare(gb, ob, actions, precision, strict_events=True):
+    tq, tv, to, tr, te = TOL[precision]
+    o_g, r_g, d_g, e_g = (v.cpu().numpy() for v in gb.step(actions))
+    o_o, r_o, d_o, e_o = ob.step(actions)
+    qg, vg = gb.state()
+    assert np.isfinite(qg).all()
+    assert np.abs(qg - ob.qpos()).max() < tq
+    assert np.abs(vg - ob.qvel()).max() < tv
+    assert np.abs(o_g - o_o).max() < to
+    assert np.abs(r_g - r_o).max() < tr
+    assert np.abs(e_g[:, CONTINUOUS] - e_o[:, CONTINUOUS]).max() < te
+    if strict_events:
+        assert np.array_equal(e_g[:, DISCRETE], e_o[:, DISCRETE])
+        assert np.array_equal(d_g.astype(bool), d_o)
+    return d_o
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+@pytest.mark.parametrize("N", [5, 8])
+def test_free_space_random_actions(precision, N):
+    n = 6
+    mdl, st = make_pair(N, 2e-3 if N == 5 else 1e-3, noise=False)
+    gb, ob = _batch(n, mdl, st, precision), OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    rng = np.random.default_rng(N)
+    for _ in range(6):
+        _compare(gb, ob, rng.integers(0, gb.n_actions - 1, n).astype(np.int32), precision)
+    gb.close()
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_objects_on_ground_and_grasp(precision):
+    """Every primitive class of the object set (box, cylinder, sphere, rounded cuboid, ellipsoid):
+    close the fingers on it, push the palm down, then terminate (lift)."""
+    n = 5
+    mdl, st = make_pair(5, 2e-3, noise=False)
+    gb, ob = _batch(n, mdl, st, precision), OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    idx = np.array([find_object(nm)[0] for nm in OBJECTS], dtype=np.int32)
+    x = np.array([0.0, 0.004, -0.004, 0.0, 0.002], dtype=np.float32)
+    r = np.array([0.0, 0.3, 0.0, 0.5, -0.2], dtype=np.float32)
+    gb.spawn_object(idx, x, -x, r); ob.spawn(idx, x, -x, r)
+    horizon = 16 if precision == "fp64" else 8
+    for t in range(horizon):
+        a = np.full(n, 1 if t < 10 else (5 if t < 14 else gb.n_actions - 1), dtype=np.int32)
+        _compare(gb, ob, a, precision)
+    assert gb.stats()["contacts"] > 0
+    gb.close()
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_noise_and_seeded_rng(precision):
+    """Sensor noise, random mean offsets and base-Z start noise come from the counter RNG
+    (seed, env id, episode, draw index): identical draws on both sides."""
+    n = 4
+    mdl, st = make_pair(5, 2e-3, noise=True, seed=99)
+    st.base_position_noise = 6e-3
+    gb, ob = _batch(n, mdl, st, precision), OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    base_z = gb.probe_field("base_z")
+    assert np.ptp(base_z) > 0, "per-env start noise missing"
+    assert np.allclose(base_z, [e.peek().base_z for e in ob.envs], atol=0)
+    rng = np.random.default_rng(3)
+    for _ in range(5):
+        _compare(gb, ob, rng.integers(0, gb.n_actions - 1, n).astype(np.int32), precision)
+    gb.close()
+
+
+def test_split_calls_equal_fused_step():
+    """set_action + action_step + observe (the reference's call sequence) == gmj_step."""
+    n = 4
+    mdl, st = make_pair(5, 2e-3, noise=True)
+    a_, b_ = _batch(n, mdl, st, "fp32"), _batch(n, mdl, st, "fp32")
+    idx = np.full(n, find_object("cube_fillet_0_3")[0], dtype=np.int32)
+    for g in (a_, b_):
+        g.reset(); g.spawn_object(idx, 0.0, 0.0, 0.0)
+    rng = np.random.default_rng(5)
+    for _ in range(4):
+        a = rng.integers(0, a_.n_actions, n).astype(np.int32)
+        o1, r1, d1, e1 = (v.clone() for v in a_.step(a))
+        b_.set_action(a); b_.action_step()
+        o2, r2, d2, e2 = b_.observe()
+        assert (o1 == o2).all() and (r1 == r2).all() and (d1 == d2).all() and (e1 == e2).all()
+    assert np.array_equal(a_.state()[0], b_.state()[0])
+    a_.close(); b_.close()
+
+
+def test_masked_reset_and_determinism():
+    n = 8
+    mdl, st = make_pair(5, 2e-3, noise=True)
+    gb = _batch(n, mdl, st, "fp32")
+    gb.reset()
+    rng = np.random.default_rng(1)
+    acts = rng.integers(0, gb.n_actions - 1, (3, n)).astype(np.int32)
+    for a in acts:
+        gb.step(a)
+    q1, _ = gb.state()
+    mask = np.array([1, 0] * (n // 2), dtype=np.uint8)
+    gb.reset(mask)
+    q2, _ = gb.state()
+    assert np.array_equal(q1[1::2], q2[1::2])            # untouched envs keep their state
+    assert not np.array_equal(q1[0::2], q2[0::2])
+    ep = gb.probe_field("episode")
+    assert (ep[0::2] == ep[1::2] + 1).all()
+    # same seeds, same actions => same trajectory bit for bit
+    g2 = _batch(n, mdl, st, "fp32")
+    g2.reset()
+    for a in acts:
+        g2.step(a)
+    assert np.array_equal(g2.state()[0], q1)
+    gb.close(); g2.close()
+
+
+def test_bad_action_is_reported():
+    from gripper_mujoco_b200.lib import GmjError
+    mdl, st = make_pair(5, 2e-3)
+    gb = _batch(2, mdl, st, "fp32")
+    gb.step(np.array([0, 99], dtype=np.int32))
+    with pytest.raises(GmjError):
+        gb.stats()
+    gb.close()
+
+
+def test_spawn_into_scene_avoids_fingertips():
+    n = 64
+    mdl, st = make_pair(5, 2e-3, noise=True)
+    gb = _batch(n, mdl, st, "fp32")
+    gb.reset()
+    gb.spawn_into_scene(0.02, 0.5)
+    q, _ = gb.state()
+    B = mdl.B
+    assert (np.abs(q[:, B:B + 2]) <= 0.02 + 1e-6).all()
+    assert (gb.probe_field("has_object") == 1).all()
+    assert len(np.unique(gb.probe_field("obj_index"))) > 8
+    gb.step(np.zeros(n, dtype=np.int32))
+    assert np.isfinite(gb.state()[0]).all()
+    gb.close()
+
+
+def test_full_size_properties():
+    """configs[1] size (4096 envs): determinism across two handles, finite state, object stays on the
+    ground under no-op-ish actions, stats add up (size-independent properties)."""
+    n = 4096
+    mdl, st = make_pair(5, 4e-3, noise=True)
+    a_, b_ = _batch(n, mdl, st, "fp32"), _batch(n, mdl, st, "fp32")
+    import torch
+    g = torch.Generator(device="cpu"); g.manual_seed(0)
+    acts = torch.randint(0, a_.n_actions - 1, (4, n), generator=g, dtype=torch.int32)
+    for gb in (a_, b_):
+        gb.reset(); gb.spawn_into_scene(0.01, 0.5)
+        for a in acts:
+            gb.step(a)
+    qa, qb = a_.state()[0], b_.state()[0]
+    assert np.isfinite(qa).all() and np.array_equal(qa, qb)
+    s = a_.stats()
+    assert s["substeps"] == n * 4 * st.sim_steps_per_action and s["unstable_resets"] == 0
+    B = mdl.B
+    assert (qa[:, B + 2] > 0).all() and (qa[:, B + 2] < 0.2).all()
+    a_.close(); b_.close()
+
+
+def test_calibration_matches_oracle_fp64():
+    """configure_settings auto-calibration (reset pose, timestep search, sim steps, wrist-Z offset,
+    gauge normalisation) over the FP64 CUDA kernels == the same flow over the oracle."""
+    from gripper_mujoco_b200.mjclass import MjClass
+    from gripper_mujoco_b200.model import GripperParams
+    from oracle.calibrate import calibrated
+    mj = MjClass(2, GripperParams(num_segments=5), precision="fp64")
+    _, s, info = calibrated(GripperParams(num_segments=5))
+    g = mj.set
+    assert g.mujoco_timestep == s.mujoco_timestep and g.sim_steps_per_action == s.sim_steps_per_action
+    assert mj.highest_stable_timestep == info["highest_stable_timestep"]
+    assert abs(g.reset_qpos_base - s.reset_qpos_base) < 1e-10 and abs(g.reset_qpos_g6 - s.reset_qpos_g6) < 1e-10
+    assert abs(g.wrist_sensor_Z.raw_value_offset - s.wrist_sensor_Z.raw_value_offset) < 1e-5
+    assert abs(g.bending_gauge.normalise / s.bending_gauge.normalise - 1) < 1e-5
+    mj.close()
+
+
+def test_mjclass_surface_fp32():
+    """Reference call sequence through the batched MjClass mirror, product precision, own calibration."""
+    import torch
+    from gripper_mujoco_b200.mjclass import MjClass
+    from gripper_mujoco_b200.model import GripperParams
+    n = 16
+    mj = MjClass(n, GripperParams(num_segments=5))
+    assert 5e-3 < mj.set.mujoco_timestep < 9e-3 and 22 <= mj.set.sim_steps_per_action <= 40
+    assert mj.get_n_actions() == 15 and mj.get_n_obs() > 0
+    mj.spawn_object(np.arange(n) * 100, 0.0, 0.0, 0.0)
+    with pytest.raises(RuntimeError):
+        mj.spawn_object(10 ** 6)
+    for t in range(3):
+        mj.set_action(torch.full((n,), 2 * t, dtype=torch.int32))
+        mj.action_step()
+        obs, rew, done = mj.get_observation(), mj.reward(), mj.is_done()
+        assert obs.shape == (n, mj.get_n_obs()) and rew.shape == (n,) and done.dtype == torch.bool
+        assert torch.isfinite(obs).all() and (obs.abs() <= 1).all()
+    names = mj.get_current_object_name()
+    assert names[1] == mj.get_object_name(100)
+    assert abs(mj.get_wrist_force()).max() < 5.0         # zeroed by the wrist-Z calibration
+    mj.close()

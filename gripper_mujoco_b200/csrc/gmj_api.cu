@@ -367,6 +367,7 @@ static int build_settings(const GmjSettings* s, DevSettings* d) {
   if (s->general[GS_use_termination_action]) d->action_options[n++] = 3 * GACT_COUNT;
   d->n_actions = n;
   double tps = s->general[GS_mujoco_timestep] * (int)s->general[GS_sim_steps_per_action];
+  int deep = 0;
   for (int k = 0; k < GSEN_COUNT; k++) {
     int is_state = (k == GSEN_motor_state || k == GSEN_base_XY || k == GSEN_base_Z || k == GSEN_base_yaw || k == GSEN_cartesian);
     if (is_state) { d->prev_steps[k] = (int)s->general[GS_state_n_prev_steps]; d->readings_per_step[k] = 1; }
@@ -376,7 +377,7 @@ static int build_settings(const GmjSettings* s, DevSettings* d) {
       double rs = t * rr;
       d->readings_per_step[k] = (int)floor(rs);
     }
-    if (1 + d->prev_steps[k] * d->readings_per_step[k] > GMJ_WIN) FAIL("sensor history deeper than the device ring (GMJ_WIN)");
+    if (1 + d->prev_steps[k] * d->readings_per_step[k] > GMJ_WIN) deep = 1;
   }
   // observation length (src/mjclass.cpp:1700-1959)
   int smode = (int)s->general[GS_sensor_sample_mode], tmode = (int)s->general[GS_state_sample_mode];
@@ -393,7 +394,10 @@ static int build_settings(const GmjSettings* s, DevSettings* d) {
   if (s->sensor[GSEN_base_Z][GSF_in_use]) no += len(GSEN_base_Z, tmode);
   if (s->sensor[GSEN_base_yaw][GSF_in_use]) no += len(GSEN_base_yaw, tmode);
   if (s->sensor[GSEN_cartesian][GSF_in_use]) no += 12 * len(GSEN_cartesian, GSM_change);
-  if (no > GMJ_MAX_OBS) FAIL("observation longer than GMJ_MAX_OBS");
+  // the reference keeps 1000 readings per sensor; the device ring keeps GMJ_WIN. Settings that need
+  // more (e.g. the timestep search runs with a stale sim_steps_per_action) can still be stepped, but
+  // asking for the observation is an error (launch_step)
+  d->obs_ok = !(deep || no > GMJ_MAX_OBS);
   d->n_obs = no;
   return 0;
 }
@@ -423,6 +427,7 @@ static int launch_step_T(GmjHandle* h, int flags, int nsub, const int32_t* actio
 }
 static int launch_step(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
                        float* reward, uint8_t* done, float* events, void* stream) {
+  if (obs && !h->hs.obs_ok) FAIL("observation unavailable: sensor history deeper than the device ring (GMJ_WIN) or longer than GMJ_MAX_OBS");
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   if (h->precision == 0) return launch_step_T<float>(h, flags, nsub, actions, frac, obs, reward, done, events, st);

@@ -83,6 +83,7 @@ struct DevSettings {
   int n_actions, action_options[32];
   int prev_steps[GSEN_COUNT], readings_per_step[GSEN_COUNT];
   int n_obs;
+  int obs_ok;   // 0: the sensor history asked for is deeper than the device ring (observation unavailable)
 };
 
 // ------------------------------------------------------------------ vec helpers
@@ -141,6 +142,9 @@ template <> __device__ __forceinline__ void sincosT<double>(double t, double* s,
 template <typename T> __device__ __forceinline__ T sqrtT(T x);
 template <> __device__ __forceinline__ float sqrtT<float>(float x) { return sqrtf(x); }
 template <> __device__ __forceinline__ double sqrtT<double>(double x) { return sqrt(x); }
+template <typename T> __device__ __forceinline__ T rsqrtT(T x);
+template <> __device__ __forceinline__ float rsqrtT<float>(float x) { return 1.0f / sqrtf(x); }
+template <> __device__ __forceinline__ double rsqrtT<double>(double x) { return 1.0 / sqrt(x); }
 template <typename T> __device__ __forceinline__ T absT(T x) { return x < 0 ? -x : x; }
 template <typename T> __device__ __forceinline__ T maxT(T a, T b) { return a > b ? a : b; }
 template <typename T> __device__ __forceinline__ T minT(T a, T b) { return a < b ? a : b; }

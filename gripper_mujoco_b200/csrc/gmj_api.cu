@@ -9,7 +9,14 @@
 #include "../../include/gmj.h"
 #include "gmj_physics.cuh"
 
-#define WARPS_PER_BLOCK 4
+// environments (warps) per block of the FP32 step kernel, one block per SM: as many as shared memory
+// holds (N = 5: 12 x 16.1 KB, 14 measured no faster, N = 8: 12 x 18.8 KB of the 227 KB)
+#ifndef GMJ_WPB_F32_N5
+#define GMJ_WPB_F32_N5 12
+#endif
+#ifndef GMJ_WPB_F32_N8
+#define GMJ_WPB_F32_N8 12
+#endif
 
 static thread_local std::string g_err;
 #define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) { g_err = std::string(#x) + ": " + cudaGetErrorString(_e); return 1; } } while (0)
@@ -23,27 +30,37 @@ template <typename T> __device__ __forceinline__ void copy_words(void* dst, cons
   for (int i = lane; i < nbytes / 4; i += 32) d[i] = s[i];
 }
 
-// One warp per environment. flags select the phases so the same kernel serves gmj_step (all),
-// gmj_set_action, gmj_action_step, gmj_substeps and gmj_observe.
+// One warp per environment, WPB environments per block. flags select the phases so the same kernel
+// serves gmj_step (all), gmj_set_action, gmj_action_step, gmj_substeps and gmj_observe.
+// The kernel is instruction-fetch bound (ncu: stall_no_inst dominates, the step is ~25 k SASS
+// instructions of mostly straight-line code against a 32 KB L1.5 I-cache), so the warps of a block
+// are kept in lockstep with a block barrier per substep: one fetch stream then feeds WPB warps.
+template <typename T, int N> struct StepCfg { static constexpr int WPB = sizeof(T) == 4 ? (N <= 5 ? GMJ_WPB_F32_N5 : GMJ_WPB_F32_N8) : 4; };
+
 template <typename T, int N>
-__global__ void __launch_bounds__(32 * WARPS_PER_BLOCK)
+__global__ void __launch_bounds__(32 * StepCfg<T, N>::WPB, 1)
 k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const DevSettings* __restrict__ Sp, int n_envs,
        int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
        float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,
        int* __restrict__ err_flag) {
+  constexpr int WPB = StepCfg<T, N>::WPB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int s_nsub_max;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int env = blockIdx.x * WARPS_PER_BLOCK + warp;
-  if (env >= n_envs) return;
+  const int env = blockIdx.x * WPB + warp;
+  const bool valid = env < n_envs;
   WarpShared<T, N>& ws = *reinterpret_cast<WarpShared<T, N>*>(smem_raw + (size_t)warp * sizeof(WarpShared<T, N>));
   const DevModel<T>& M = *Mp; const DevSettings& S = *Sp;
-  copy_words<T>(&ws.e, &envs[env], sizeof(EnvState<T>), lane);
-  if (lane == 0) { ws.ax.ncon = 0; ws.ax.nrow = 0; ws.ax.niter = 0; ws.ax.wrist_z = ws.e.wrist_z; }
-  ws.qfk[lane] = ws.e.qpos[lane];
-  __syncwarp();
+  if (threadIdx.x == 0) s_nsub_max = 0;
+  if (valid) {
+    copy_words<T>(&ws.e, &envs[env], sizeof(EnvState<T>), lane);
+    if (lane == 0) { ws.ax.ncon = 0; ws.ax.nrow = 0; ws.ax.niter = 0; ws.ax.wrist_z = ws.e.wrist_z; }
+    ws.qfk[lane] = ws.e.qpos[lane];
+  }
+  __syncthreads();
   EnvState<T>& e = ws.e;
   int extra = 0;
-  if (flags & STEP_SET_ACTION) {
+  if ((flags & STEP_SET_ACTION) && valid) {
     if (lane == 0) {
       extra = set_action<T>(e, S, M, actions[env], frac ? frac[env] : 0.0f);
       if (extra < 0) { extra = 0; if (err_flag) atomicExch(err_flag, 1); }
@@ -52,22 +69,30 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
     __syncwarp();
   }
   if (flags & STEP_SUBSTEPS) {
-    const int nsub = extra + (nsub_override >= 0 ? nsub_override : (int)S.s.general[GS_sim_steps_per_action]);
+    const int nsub = valid ? extra + (nsub_override >= 0 ? nsub_override : (int)S.s.general[GS_sim_steps_per_action]) : 0;
+    if (lane == 0) atomicMax(&s_nsub_max, nsub);
+    __syncthreads();
+    const int nsub_max = s_nsub_max;
     const double dtd = S.s.general[GS_mujoco_timestep];
     const bool curve = S.s.general[GS_curve_validation] != 0;
     const T tipf = curve ? (T)S.s.general[GS_tip_force_applied] : T(0);
-    for (int i = 0; i < nsub; i++) {
-      if (curve && lane == 0) for (int id = 0; id < 6; id++) set_weld<T, N>(e, id, 1, ws.qfk);   // apply_segment_force re-locks every step
-      __syncwarp();
-      physics_substep<T, N>(ws, M, S, lane, dtd, tipf);
-      if (lane == 0) {
-        update_all<T, N>(e, ws.qfk);
-        if (flags & STEP_SENSORS) monitor_sensors<T, N>(e, S, M, ws.ax);
-      }
-      __syncwarp();
+    for (int i = 0; i < nsub_max; i++) {
+      __syncthreads();                       // lockstep: shared instruction stream
+      if (i < nsub) {
+        if (curve && lane == 0) for (int id = 0; id < 6; id++) set_weld<T, N>(e, id, 1, ws.qfk);   // apply_segment_force re-locks every step
+        __syncwarp();
+        physics_substep<T, N, 32 * WPB>(ws, M, S, lane, dtd, tipf);
+        phase_barrier<32 * WPB>(GMJ_NPHASE);
+        if (lane == 0) {
+          update_all<T, N>(e, ws.qfk);
+          if (flags & STEP_SENSORS) monitor_sensors<T, N>(e, S, M, ws.ax);
+        }
+        __syncwarp();
+      } else { phase_idle<32 * WPB>(); phase_barrier<32 * WPB>(GMJ_NPHASE); }
     }
-    if (lane == 0) e.wrist_z = (float)ws.ax.wrist_z;
+    if (valid && lane == 0) e.wrist_z = (float)ws.ax.wrist_z;
   }
+  if (!valid) return;
   if ((flags & STEP_TAIL) && lane == 0) {
     sense_gripper_state<T>(e, S, M);
     update_env<T>(e, S, ws.ax);
@@ -406,11 +431,12 @@ static int build_settings(const GmjSettings* s, DevSettings* d) {
 template <typename T, int N>
 static int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
                           float* reward, uint8_t* done, float* events, cudaStream_t st) {
-  size_t smem = sizeof(WarpShared<T, N>) * WARPS_PER_BLOCK;
+  constexpr int WPB = StepCfg<T, N>::WPB;
+  size_t smem = sizeof(WarpShared<T, N>) * WPB;
   static bool attr_set = false;
   if (!attr_set) { CK(cudaFuncSetAttribute(k_step<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
-  int blocks = (h->n_envs + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
-  k_step<T, N><<<blocks, 32 * WARPS_PER_BLOCK, smem, st>>>((EnvState<T>*)h->envs, (const DevModel<T>*)h->model, h->settings,
+  int blocks = (h->n_envs + WPB - 1) / WPB;
+  k_step<T, N><<<blocks, 32 * WPB, smem, st>>>((EnvState<T>*)h->envs, (const DevModel<T>*)h->model, h->settings,
       h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag);
   CK(cudaGetLastError());
   h->smem_bytes = smem;
@@ -421,7 +447,9 @@ static int launch_step_T(GmjHandle* h, int flags, int nsub, const int32_t* actio
                          float* reward, uint8_t* done, float* events, cudaStream_t st) {
   switch (h->N) {
     case 5: return launch_step_TN<T, 5>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
+#ifndef GMJ_ONLY_F5            // development switch: compile one instantiation only
     case 8: return launch_step_TN<T, 8>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
+#endif
     default: FAIL("this build instantiates the step kernel for N = 5 and N = 8 segments only");
   }
 }
@@ -431,7 +459,11 @@ static int launch_step(GmjHandle* h, int flags, int nsub, const int32_t* actions
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   if (h->precision == 0) return launch_step_T<float>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
+#ifndef GMJ_ONLY_F5
   return launch_step_T<double>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
+#else
+  FAIL("built with GMJ_ONLY_F5");
+#endif
 }
 static size_t env_bytes(const GmjHandle* h) { return h->precision == 0 ? sizeof(EnvState<float>) : sizeof(EnvState<double>); }
 

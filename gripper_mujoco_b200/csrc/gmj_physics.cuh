@@ -16,20 +16,24 @@
 #include "gmj_collide.cuh"
 #include "gmj_tail.cuh"
 
-#define GMJ_WS 41   // row stride of W (odd: conflict-free when lanes walk rows)
-#define GMJ_AS 49   // row stride of A
-
 template <typename T, int N>
 struct WarpShared {
+  static constexpr int B = 3 * N + 8;
+  static constexpr int NW = B + 6;          // whitened row: B gripper columns (lane order) + 6 object columns
+  static constexpr int WS = NW | 1;         // odd stride: conflict-free when lanes walk rows
   EnvState<T> e;
   WarpAux<T> ax;
-  T W[GMJ_RMAX + 1][GMJ_WS];        // whitened rows; row nrow holds the whitened smooth force
-  T A[GMJ_RMAX][GMJ_AS];            // A[r][c], c = nrow column holds W_r . w_s
+  T W[GMJ_RMAX + 1][WS];            // whitened rows; row nrow holds the whitened smooth force
+  T A[GMJ_RMAX * (GMJ_RMAX + 1) / 2]; // packed lower triangle of W W^T, overwritten by its Cholesky factor
+  T u[WS + 1];                      // W^T f scratch of the LCP solver
   T L2[3][N + 2][N + 3];            // second factor, for column access in the back substitution
   T qfk[40];                        // qpos of the last kinematics pass (weld anchors)
   T rpos[GMJ_RMAX], rjv[GMJ_RMAX], rmu[GMJ_RMAX];
   int rtype[GMJ_RMAX], rfirst[GMJ_RMAX], rlane[GMJ_RMAX];
 };
+// packed lower-triangular index; consecutive rows start at triangular numbers, which are all distinct
+// mod 32 over any 32 consecutive rows, so "lane i reads L[i][k]" is bank-conflict free
+#define TRI(i, j) (((i) * ((i) + 1) >> 1) + (j))
 
 enum { ROW_EQ = 0, ROW_LIMIT = 1, ROW_CONTACT = 2 };
 
@@ -158,10 +162,10 @@ __device__ __forceinline__ void emit_row(WarpShared<T, N>& ws, const Topo<N>& tp
                                          const T* rsqo, int r, T Jl, const T* Jo, int type, T pos, T jv, T mu,
                                          int first, int jl) {
   T x = ldl_fwd<T, N>(tp, Lrow, lb, Jl) * rsq;
-  ws.W[r][tp.lane] = tp.act ? x : T(0);
+  if (tp.act) ws.W[r][tp.lane] = x;
   if (tp.lane == 0) {
 #pragma unroll
-    for (int k = 0; k < 6; k++) ws.W[r][32 + k] = Jo[k] * rsqo[k];
+    for (int k = 0; k < 6; k++) ws.W[r][3 * N + 8 + k] = Jo[k] * rsqo[k];
     ws.rtype[r] = type; ws.rpos[r] = pos; ws.rjv[r] = jv; ws.rmu[r] = mu; ws.rfirst[r] = first; ws.rlane[r] = jl;
   }
 }
@@ -180,41 +184,85 @@ __device__ __forceinline__ T jac_entry(const Topo<N>& tp, int bl, V3<T> p, V3<T>
 }
 
 
+// ------------------------------------------------------------------ A = W W^T, packed lower triangle
+// Lane owns rows lane and lane + 32 and computes columns cc <= row. bcol (optional) = W_r . W[nr] (the
+// whitened smooth force), the extra column of the dual.
+template <typename T, int N>
+__device__ void form_A(WarpShared<T, N>& ws, int nr, int lane, T* bcol) {
+  constexpr int NW = WarpShared<T, N>::NW;
+#pragma unroll 1
+  for (int slot = 0; slot < 2; slot++) {
+    const int r = lane + 32 * slot;
+    if (bcol) bcol[slot] = 0;
+    if (slot == 1 && nr <= 32) break;
+    const bool own = r < nr;
+    T wr[NW];
+#pragma unroll
+    for (int k = 0; k < NW; k++) wr[k] = own ? ws.W[r][k] : T(0);
+    const int top = nr - 1 < 31 + 32 * slot ? nr - 1 : 31 + 32 * slot;     // largest owned row of this slot in the warp
+    for (int cc = 0; cc <= top; cc++) {
+      T a0 = 0, a1 = 0;
+#pragma unroll
+      for (int k = 0; k + 1 < NW; k += 2) { a0 += wr[k] * ws.W[cc][k]; a1 += wr[k + 1] * ws.W[cc][k + 1]; }
+      if (NW & 1) a0 += wr[NW - 1] * ws.W[cc][NW - 1];
+      if (own && cc <= r) ws.A[TRI(r, cc)] = a0 + a1;
+    }
+    if (bcol) {
+      T a0 = 0, a1 = 0;
+#pragma unroll
+      for (int k = 0; k + 1 < NW; k += 2) { a0 += wr[k] * ws.W[nr][k]; a1 += wr[k + 1] * ws.W[nr][k + 1]; }
+      if (NW & 1) a0 += wr[NW - 1] * ws.W[nr][NW - 1];
+      bcol[slot] = a0 + a1;
+    }
+  }
+}
+
 // ------------------------------------------------------------------ dense LCP solver (warp)
-// A: symmetric, full on entry; the strict lower triangle is overwritten by the Cholesky factor of the
-// active principal submatrix, the upper triangle (and the diagonal) keep the original entries.
-// Lane owns rows lane and lane + 32. b, R, type, f are per owned row (slot 0/1). Returns the number
-// of pivoting rounds.
-template <typename T>
-__device__ int lcp_solve(T (*A)[GMJ_AS], int nr, int lane, const T* b, const T* R, const int* type, T* f, bool warm) {
+// (A + R) f + b = w; equality rows: w = 0; inequality rows: f >= 0, w >= 0, f w = 0. Block principal
+// pivoting over the active set; each round factors the active principal submatrix in place (packed
+// lower triangle of ws.A, left-looking so column j still holds the original entries when it is
+// reached) and gets w on the inactive rows from W (w = W (W^T f) + b). A second round has to rebuild
+// A from W first; with the warm-started active set that happens in about 1 % of the substeps.
+// Lane owns rows lane and lane + 32; b, R, type, f are per owned row. Returns the number of rounds.
+template <typename T, int N>
+__device__ int lcp_solve(WarpShared<T, N>& ws, int nr, int lane, const T* b, const T* R, const int* type, T* f, bool warm) {
+  constexpr int NW = WarpShared<T, N>::NW;
+  T* A = ws.A;
   const T eps = sizeof(T) == 8 ? T(1e-12) : T(2e-6);
   const int maxit = 40;
   const int r0 = lane, r1 = lane + 32;
   const bool two = nr > 32;
-  // active flags per owned row
   bool act0, act1;
   act0 = r0 < nr && (type[0] == ROW_EQ || (warm ? f[0] > 0 : b[0] < 0));
   act1 = r1 < nr && (type[1] == ROW_EQ || (warm ? f[1] > 0 : b[1] < 0));
-  const T d0 = r0 < nr ? A[r0][r0] + R[0] : T(1), d1 = r1 < nr ? A[r1][r1] + R[1] : T(1);
   T bscale = warp_max(maxT<T>(r0 < nr ? absT<T>(b[0]) : T(0), r1 < nr ? absT<T>(b[1]) : T(0)));
   int best = 1 << 30, patience = 3, it = 0;
   T x0 = 0, x1 = 0;
   for (;; ) {
+    if (it > 0) { __syncwarp(); form_A<T, N>(ws, nr, lane, nullptr); __syncwarp(); }
     it++;
     const unsigned m0 = __ballot_sync(GMJ_FULL, act0), m1 = __ballot_sync(GMJ_FULL, act1);
     // ---- left-looking Cholesky of K_FF (identity on the inactive rows), column j
     T ld0 = 1, ld1 = 1;                       // 1 / L[r][r] of the owned rows
+    const int t0 = TRI(r0, 0), t1 = TRI(r1, 0);
     for (int j = 0; j < nr; j++) {
       const bool jact = j < 32 ? ((m0 >> j) & 1) : ((m1 >> (j - 32)) & 1);
+      const int tj = TRI(j, 0);
       T s0 = 0, s1 = 0;
       if (jact) {
         if (act0 && r0 >= j) {
-          s0 = (r0 == j) ? d0 : A[j][r0];
-          for (int k = 0; k < j; k++) s0 -= A[r0][k] * A[j][k];
+          T a = A[t0 + j], c = 0;
+          int k = 0;
+          for (; k + 1 < j; k += 2) { a -= A[t0 + k] * A[tj + k]; c -= A[t0 + k + 1] * A[tj + k + 1]; }
+          if (k < j) a -= A[t0 + k] * A[tj + k];
+          s0 = a + c + (r0 == j ? R[0] : T(0));
         }
         if (two && act1 && r1 >= j) {
-          s1 = (r1 == j) ? d1 : A[j][r1];
-          for (int k = 0; k < j; k++) s1 -= A[r1][k] * A[j][k];
+          T a = A[t1 + j], c = 0;
+          int k = 0;
+          for (; k + 1 < j; k += 2) { a -= A[t1 + k] * A[tj + k]; c -= A[t1 + k + 1] * A[tj + k + 1]; }
+          if (k < j) a -= A[t1 + k] * A[tj + k];
+          s1 = a + c + (r1 == j ? R[1] : T(0));
         }
       }
       T dj = __shfl_sync(GMJ_FULL, j < 32 ? s0 : s1, j & 31);
@@ -222,8 +270,8 @@ __device__ int lcp_solve(T (*A)[GMJ_AS], int nr, int lane, const T* b, const T* 
       if (r0 == j) ld0 = inv;
       if (r1 == j) ld1 = inv;
       __syncwarp();
-      if (r0 > j && r0 < nr) A[r0][j] = s0 * inv;
-      if (two && r1 > j && r1 < nr) A[r1][j] = s1 * inv;
+      if (r0 > j && r0 < nr) A[t0 + j] = s0 * inv;
+      if (two && r1 > j && r1 < nr) A[t1 + j] = s1 * inv;
       __syncwarp();
     }
     // ---- forward substitution L y = -b_F
@@ -232,25 +280,35 @@ __device__ int lcp_solve(T (*A)[GMJ_AS], int nr, int lane, const T* b, const T* 
       T yj = __shfl_sync(GMJ_FULL, j < 32 ? y0 * ld0 : y1 * ld1, j & 31);
       if (r0 == j) y0 = yj;
       if (r1 == j) y1 = yj;
-      if (r0 > j && r0 < nr) y0 -= A[r0][j] * yj;
-      if (two && r1 > j && r1 < nr) y1 -= A[r1][j] * yj;
+      if (r0 > j && r0 < nr) y0 -= A[t0 + j] * yj;
+      if (two && r1 > j && r1 < nr) y1 -= A[t1 + j] * yj;
     }
     // ---- back substitution L^T x = y
     for (int j = nr - 1; j >= 0; j--) {
       T xj = __shfl_sync(GMJ_FULL, j < 32 ? y0 * ld0 : y1 * ld1, j & 31);
       if (r0 == j) y0 = xj;
       if (r1 == j) y1 = xj;
-      if (r0 < j) y0 -= A[j][r0] * xj;
-      if (two && r1 < j) y1 -= A[j][r1] * xj;
+      const int tj = TRI(j, 0);
+      if (r0 < j) y0 -= A[tj + r0] * xj;
+      if (two && r1 < j) y1 -= A[tj + r1] * xj;
     }
     x0 = act0 ? y0 : T(0); x1 = act1 ? y1 : T(0);
-    // ---- w = A_orig x + b on the inactive rows (original A: upper triangle + symmetry)
-    T w0 = r0 < nr ? b[0] : T(0), w1 = r1 < nr ? b[1] : T(0);
-    for (int c = 0; c < nr; c++) {
-      T xc = __shfl_sync(GMJ_FULL, c < 32 ? x0 : x1, c & 31);
-      if (r0 < nr && c != r0) w0 += (c < r0 ? A[c][r0] : A[r0][c]) * xc;
-      if (two && r1 < nr && c != r1) w1 += (c < r1 ? A[c][r1] : A[r1][c]) * xc;
+    // ---- w = W (W^T x) + b on the inactive rows
+    {
+      T u0 = 0, u1 = 0;                        // columns lane and lane + 32 of W^T x
+      const bool c0 = lane < NW, c1 = lane + 32 < NW;
+      for (int c = 0; c < nr; c++) {
+        T xc = __shfl_sync(GMJ_FULL, c < 32 ? x0 : x1, c & 31);
+        if (c0) u0 += ws.W[c][lane] * xc;
+        if (c1) u1 += ws.W[c][lane + 32] * xc;
+      }
+      if (c0) ws.u[lane] = u0;
+      if (c1) ws.u[lane + 32] = u1;
+      __syncwarp();
     }
+    T w0 = r0 < nr ? b[0] : T(0), w1 = r1 < nr ? b[1] : T(0);
+    if (r0 < nr && !act0) { T a = 0; for (int k = 0; k < NW; k++) a += ws.W[r0][k] * ws.u[k]; w0 += a; }
+    if (two && r1 < nr && !act1) { T a = 0; for (int k = 0; k < NW; k++) a += ws.W[r1][k] * ws.u[k]; w1 += a; }
     T fscale = warp_max(maxT<T>(absT<T>(x0), absT<T>(x1)));
     const T tolf = eps * (1 + fscale), tolw = eps * (1 + bscale);
     bool bad0 = r0 < nr && type[0] != ROW_EQ && (act0 ? x0 < -tolf : w0 < -tolw);
@@ -274,17 +332,35 @@ __device__ int lcp_solve(T (*A)[GMJ_AS], int nr, int lane, const T* b, const T* 
   return it;
 }
 
-template <typename T, int N>
+// ------------------------------------------------------------------ block lockstep
+// The substep is ~10 k straight-line SASS instructions per warp against a 32 KB L1.5 I-cache, so it
+// runs at the speed of instruction fetch. Phase barriers keep the warps of a block on the same code
+// so that one fetch stream feeds all of them. Barrier 1 is used (0 is __syncthreads in the caller);
+// warps that skip a substep (finished, frozen) call phase_idle() to pass the same barriers.
+#ifndef GMJ_PHASE_MASK
+#define GMJ_PHASE_MASK 0x3ff
+#endif
+#define GMJ_NPHASE 9
+template <int NT> __device__ __forceinline__ void phase_barrier(int id) {
+  if ((GMJ_PHASE_MASK >> id) & 1) asm volatile("bar.sync 1, %0;" :: "n"(NT) : "memory");
+}
+template <int NT> __device__ __forceinline__ void phase_idle() {
+#pragma unroll
+  for (int id = 0; id < GMJ_NPHASE; id++) phase_barrier<NT>(id);
+}
+
+template <typename T, int N, int NT>
 __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, const DevSettings& S, int lane, double dtd, T tip_force) {
   const T dt = (T)dtd;
   constexpr int NL = N + 2, B = 3 * N + 8, PALM = 3 * N + 7;
   const Topo<N> tp(lane);
   EnvState<T>& e = ws.e;
   // after a BADQACC-class failure the env is frozen until the caller resets it (is_done reports it)
-  if (e.unstable) { __syncwarp(); if (lane == 0) e.time += dtd; __syncwarp(); return; }
+  if (e.unstable) { __syncwarp(); if (lane == 0) e.time += dtd; __syncwarp(); phase_idle<NT>(); return; }
   const T gz = -M.zref;                                   // ground plane height in shifted coordinates
 
   // ------------------------------------------------------------------ kinematics
+  phase_barrier<NT>(0);
   T q = tp.act ? e.qpos[lane] : T(0), qd = tp.act ? e.qvel[lane] : T(0);
   ws.qfk[lane] = q;
   M3<T> Rl; V3<T> pl = mk<T>(M.f[MF_pos0][lane], M.f[MF_pos1][lane], M.f[MF_pos2][lane]);
@@ -324,6 +400,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   const V3<T> oI = mk<T>(e.obj[10], e.obj[11], e.obj[12]);
 
   // ------------------------------------------------------------------ spatial quantities
+  phase_barrier<NT>(1);
   T mass = tp.act ? M.f[MF_mass][lane] : T(0);
   V3<T> c = p + mul(R, mk<T>(M.f[MF_ip0][lane], M.f[MF_ip1][lane], M.f[MF_ip2][lane]));
   SpI<T> I;
@@ -396,6 +473,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   T Mb = (lane != 0 && tp.act) ? spdot(Sb, F) : T(0);
 
   // ------------------------------------------------------------------ control + smooth forces
+  phase_barrier<NT>(2);
   // luke::control_gripper / control_base (src/myfunctions.cpp:1965-2057)
   T damp = tp.act ? M.f[MF_damp][lane] : T(0), stiff = tp.act ? M.f[MF_stiff][lane] : T(0);
   T ctrl = 0;
@@ -440,6 +518,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   }
 
   // ------------------------------------------------------------------ factorisations
+  phase_barrier<NT>(3);
   T M2row[NL];
 #pragma unroll
   for (int k = 0; k < NL; k++) M2row[k] = Mrow[k] + ((k == tp.local && tp.act) ? dt * damp : T(0));
@@ -458,6 +537,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   __syncwarp();
 
   // ------------------------------------------------------------------ collision
+  phase_barrier<NT>(4);
   int ncon = 0;
   Shape<T> so;
   so.type = (int)e.obj[0]; so.size = mk<T>(e.obj[1], e.obj[2], e.obj[3]); so.round = e.obj[4];
@@ -559,6 +639,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   __syncwarp();
 
   // ------------------------------------------------------------------ constraint rows
+  phase_barrier<NT>(5);
   int nr = 0;
   const T zero6[6] = { 0, 0, 0, 0, 0, 0 };
   // welds: joint `j` locked at its anchor; rows = world components of the joint axis
@@ -638,32 +719,20 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
     nr += 4;
   }
   // whitened smooth force as row nr
-  ws.W[nr][lane] = tp.act ? wsm : T(0);
+  if (tp.act) ws.W[nr][lane] = wsm;
   if (lane == 0) {
 #pragma unroll
-    for (int k = 0; k < 6; k++) ws.W[nr][32 + k] = tauo[k] * rsqo[k];
+    for (int k = 0; k < 6; k++) ws.W[nr][B + k] = tauo[k] * rsqo[k];
     ws.ax.ncon = ncon; ws.ax.nrow = nr;
   }
   __syncwarp();
 
   // ------------------------------------------------------------------ A = W W^T (+ column W . w_s)
+  phase_barrier<NT>(6);
   // lane owns rows r0 = lane and r1 = lane + 32
   const int r0 = lane, r1 = lane + 32;
-#pragma unroll 1
-  for (int slot = 0; slot < 2; slot++) {
-    int r = slot ? r1 : r0;
-    if (slot == 1 && nr <= 32) break;
-    bool own = r < nr;
-    T wr[38];
-#pragma unroll
-    for (int k = 0; k < 38; k++) wr[k] = own ? ws.W[r][k] : T(0);
-    for (int cc = 0; cc <= nr; cc++) {
-      T acc = 0;
-#pragma unroll
-      for (int k = 0; k < 38; k++) acc += wr[k] * ws.W[cc][k];
-      if (own) ws.A[r][cc] = acc;
-    }
-  }
+  T bcol[2];
+  form_A<T, N>(ws, nr, lane, bcol);
   __syncwarp();
   // regulariser, reference acceleration, PGS state per owned row
   T pf[2], py[2], pb[2], pR[2], pinv[2]; int ptype[2];
@@ -679,37 +748,39 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
         T imp = impedance<T>(M.solimp, pos);
         T aref = -bb * ws.rjv[r] - kk * imp * pos;
         int type = ws.rtype[r];
-        T Arr = ws.A[r][r], Rv;
+        T Arr = ws.A[TRI(r, r)], Rv;
         if (type == ROW_CONTACT) {
           int rf = ws.rfirst[r]; T mu = ws.rmu[r];
-          T Ann = T(0.25) * (ws.A[rf][rf] + ws.A[rf + 1][rf + 1] + 2 * ws.A[rf][rf + 1]);
+          T Ann = T(0.25) * (ws.A[TRI(rf, rf)] + ws.A[TRI(rf + 1, rf + 1)] + 2 * ws.A[TRI(rf + 1, rf)]);
           Rv = 2 * mu * mu * (1 - imp) / imp * (1 + mu * mu) * Ann;
         } else Rv = (1 - imp) / imp * Arr;
         Rv = maxT<T>(Rv, T(1e-15));
-        pR[slot] = Rv; pinv[slot] = T(1) / (Arr + Rv); pb[slot] = ws.A[r][nr] - aref; ptype[slot] = type;
+        pR[slot] = Rv; pinv[slot] = T(1) / (Arr + Rv); pb[slot] = bcol[slot] - aref; ptype[slot] = type;
         pf[slot] = (e.nrow_prev == nr) ? e.fprev[r] : T(0);
       }
     }
   }
   __syncwarp();
   // ------------------------------------------------------------------ dual LCP, direct
+  phase_barrier<NT>(7);
   // (A + R) f + b = w, equality rows w = 0, inequality rows f >= 0, w >= 0, f w = 0. A + R is SPD so
   // the solution is unique: the oracle reaches it with PGS converged to 1e-13, here it is found by
   // block principal pivoting over the active set (warm-started from the previous substep) with an
   // in-place warp Cholesky per pivot -- a few thousand cycles instead of hundreds of GS sweeps.
   int iters = 0;
-  if (nr > 0) iters = lcp_solve<T>(ws.A, nr, lane, pb, pR, ptype, pf, e.nrow_prev == nr);
+  if (nr > 0) iters = lcp_solve<T, N>(ws, nr, lane, pb, pR, ptype, pf, e.nrow_prev == nr);
   if (r0 < nr) e.fprev[r0] = pf[0];
   if (r1 < nr) e.fprev[r1] = pf[1];
   if (lane == 0) { e.nrow_prev = nr; ws.ax.niter = iters; }
   __syncwarp();
 
   // ------------------------------------------------------------------ constraint force, integration
+  phase_barrier<NT>(8);
   T g = 0, go = 0;
   for (int r = 0; r < nr; r++) {
     T fr = e.fprev[r];
-    g += ws.W[r][lane] * fr;
-    if (lane < 6) go += ws.W[r][32 + lane] * fr;
+    if (tp.act) g += ws.W[r][lane] * fr;
+    if (lane < 6) go += ws.W[r][B + lane] * fr;
   }
   // tau_c = L D^1/2 g
   T tauc = ldl_mulL<T, N>(tp, Mrow, lb, tp.act ? g * sqrtT<T>(D) : T(0));

@@ -11,7 +11,8 @@ from .model import GmjModel, GmjObject
 from .settings import GmjSettings
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libgripper_b200.so")
+# GMJ_LIB: development override to A/B-test differently compiled builds of the same sources
+SO_PATH = os.environ.get("GMJ_LIB") or os.path.join(_HERE, "libgripper_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
 SOURCES = ["gmj_api.cu", "gmj_physics.cuh", "gmj_tail.cuh", "gmj_collide.cuh", "gmj_device.cuh"]
 HEADERS = [os.path.join(_HERE, "..", "include", h) for h in ("gmj.h", "gmj_types.h")]

@@ -5,7 +5,8 @@
   python bench.py --impl reference --gpus N ...            reference arm: CPU pool on the host cores
 
 One "step" = one action-step of every env of the rank: set_action + S physics substeps +
-sensors + events + observation + reward + done (gmj_step, one launch), followed by the masked
+sensors + events + observation + reward + done (gmj_step: k_step set_action pass + k_step
+physics pass), followed by the masked
 auto-reset + object respawn of finished episodes (gmj_reset + gmj_spawn), as MjEnv.step/reset do.
 """
 from __future__ import annotations
@@ -199,7 +200,7 @@ def main():
         m8 = mask.to(torch.uint8)
         gb.reset(m8); gb.spawn_into_scene(0.01, float(np.pi / 2), m8)      # MjEnv.reset: reset -> spawn
         ep_steps.mul_((~mask).to(torch.int32))
-        launches[0] += 3
+        launches[0] += 4
         return obs, rew, done
 
     mj.spawn_into_scene(0.01, float(np.pi / 2))
@@ -227,7 +228,7 @@ def main():
         gb.reset(m8); gb.spawn_into_scene(0.01, float(np.pi / 2), m8)
         ep_steps.mul_((~mask).to(torch.int32))
         evs[k][2].record()
-        launches[0] += 3
+        launches[0] += 4
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()

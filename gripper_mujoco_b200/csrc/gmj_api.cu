@@ -23,7 +23,10 @@ static thread_local std::string g_err;
 #define FAIL(msg) do { g_err = (msg); return 1; } while (0)
 
 // ------------------------------------------------------------------------------------------ kernels
-enum { STEP_SET_ACTION = 1, STEP_SUBSTEPS = 2, STEP_TAIL = 4, STEP_OUTPUT = 8, STEP_SENSORS = 16 };
+enum { STEP_SET_ACTION = 1, STEP_SUBSTEPS = 2, STEP_TAIL = 4, STEP_OUTPUT = 8, STEP_SENSORS = 16,
+       STEP_COLLECT = 32,   // set_action only: append envs that owe extra substeps (termination lift) to env_list
+       STEP_LIST = 64,      // run on the envs of env_list[0 .. *env_count) instead of all envs
+       STEP_COMBINED = 128 }; // blocks [0, list_blocks) take env_list (owed lift substeps first), the rest all other envs
 
 template <typename T> __device__ __forceinline__ void copy_words(void* dst, const void* src, int nbytes, int lane) {
   const uint32_t* s = (const uint32_t*)src; uint32_t* d = (uint32_t*)dst;
@@ -42,13 +45,22 @@ __global__ void __launch_bounds__(32 * StepCfg<T, N>::WPB, 1)
 k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const DevSettings* __restrict__ Sp, int n_envs,
        int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
        float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,
-       int* __restrict__ err_flag) {
+       int* __restrict__ err_flag, int* __restrict__ env_list, int* __restrict__ env_count, int list_blocks) {
   constexpr int WPB = StepCfg<T, N>::WPB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_nsub_max;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int env = blockIdx.x * WPB + warp;
-  const bool valid = env < n_envs;
+  int bid = blockIdx.x;
+  bool list_block = (flags & STEP_LIST) != 0;
+  if (flags & STEP_COMBINED) { list_block = bid < list_blocks; if (!list_block) bid -= list_blocks; }
+  int env = bid * WPB + warp;
+  bool valid = env < n_envs;
+  if (list_block) {                        // dense blocks over the collected envs; surplus blocks leave at once
+    const int cnt = *env_count;
+    if (bid * WPB >= cnt) return;
+    valid = env < cnt;
+    env = valid ? env_list[env] : 0;
+  } else if ((flags & STEP_COMBINED) && valid) valid = envs[env].pending_extra == 0;
   WarpShared<T, N>& ws = *reinterpret_cast<WarpShared<T, N>*>(smem_raw + (size_t)warp * sizeof(WarpShared<T, N>));
   const DevModel<T>& M = *Mp; const DevSettings& S = *Sp;
   if (threadIdx.x == 0) s_nsub_max = 0;
@@ -65,8 +77,17 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
       extra = set_action<T>(e, S, M, actions[env], frac ? frac[env] : 0.0f);
       if (extra < 0) { extra = 0; if (err_flag) atomicExch(err_flag, 1); }
     }
+    if ((flags & STEP_COLLECT) && lane == 0) {
+      e.pending_extra = extra;
+      if (extra > 0) env_list[atomicAdd(env_count, 1)] = env;
+    }
     extra = __shfl_sync(GMJ_FULL, extra, 0);
     __syncwarp();
+  }
+  if (list_block && valid) {               // owed lift substeps run first, exactly as inside MjClass::set_action
+    extra = (int)e.pending_extra;
+    __syncwarp();
+    if (lane == 0) e.pending_extra = 0;
   }
   if (flags & STEP_SUBSTEPS) {
     const int nsub = valid ? extra + (nsub_override >= 0 ? nsub_override : (int)S.s.general[GS_sim_steps_per_action]) : 0;
@@ -307,6 +328,7 @@ struct GmjHandle {
   DevSettings hs;        // host copy
   GmjObject* objects; int n_objects;
   int* err_flag;
+  int* env_list; int* env_count;   // envs that owe the 2S termination-lift substeps this step
   unsigned long long* stats_dev;
   double* scratch; size_t scratch_len;
   GmjModel hm;
@@ -431,13 +453,15 @@ static int build_settings(const GmjSettings* s, DevSettings* d) {
 template <typename T, int N>
 static int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
                           float* reward, uint8_t* done, float* events, cudaStream_t st) {
+  const bool combined = (flags & STEP_COMBINED) != 0;
   constexpr int WPB = StepCfg<T, N>::WPB;
   size_t smem = sizeof(WarpShared<T, N>) * WPB;
   static bool attr_set = false;
   if (!attr_set) { CK(cudaFuncSetAttribute(k_step<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
   int blocks = (h->n_envs + WPB - 1) / WPB;
-  k_step<T, N><<<blocks, 32 * WPB, smem, st>>>((EnvState<T>*)h->envs, (const DevModel<T>*)h->model, h->settings,
-      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag);
+  const int list_blocks = combined ? blocks : 0;      // worst case every env owes a lift; empty list blocks exit at once
+  k_step<T, N><<<blocks + list_blocks, 32 * WPB, smem, st>>>((EnvState<T>*)h->envs, (const DevModel<T>*)h->model, h->settings,
+      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks);
   CK(cudaGetLastError());
   h->smem_bytes = smem;
   return 0;
@@ -501,6 +525,8 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
   CK(cudaMalloc(&h->settings, sizeof(DevSettings)));
   CK(cudaMalloc(&h->err_flag, sizeof(int))); CK(cudaMemset(h->err_flag, 0, sizeof(int)));
   CK(cudaMalloc(&h->stats_dev, 8 * sizeof(unsigned long long)));
+  CK(cudaMalloc(&h->env_list, sizeof(int) * (size_t)n_envs)); CK(cudaMalloc(&h->env_count, sizeof(int)));
+  CK(cudaMemset(h->env_count, 0, sizeof(int)));
   if (gmj_set_settings(h, settings)) { return 1; }
   *out = h;
   return gmj_reset(h, nullptr, nullptr);
@@ -509,7 +535,7 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
 int gmj_destroy(GmjHandle* h) {
   if (!h) return 0;
   cudaSetDevice(h->device);
-  cudaFree(h->envs); cudaFree(h->model); cudaFree(h->settings); cudaFree(h->err_flag); cudaFree(h->stats_dev);
+  cudaFree(h->envs); cudaFree(h->model); cudaFree(h->settings); cudaFree(h->err_flag); cudaFree(h->stats_dev); cudaFree(h->env_list); cudaFree(h->env_count);
   if (h->objects) cudaFree(h->objects);
   if (h->scratch) cudaFree(h->scratch);
   delete h;
@@ -551,16 +577,30 @@ int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const 
   return 0;
 }
 
+// set_action for every env, then the termination action's 2 x sim_steps_per_action lift substeps
+// (quirk Q8: they run INSIDE MjClass::set_action) on a compacted list of just those envs -- in the
+// lockstep kernel a single lifting env would otherwise hold its whole block for 3S substeps.
+// Pass 1: set_action for every env; envs that owe the termination action's 2 x sim_steps_per_action lift
+// substeps (quirk Q8: they run INSIDE MjClass::set_action) are recorded in env_list / pending_extra.
+static int launch_collect(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, void* stream) {
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemsetAsync(h->env_count, 0, sizeof(int), (cudaStream_t)stream));
+  return launch_step(h, STEP_SET_ACTION | STEP_COLLECT, 0, actions_dev, frac_dev, nullptr, nullptr, nullptr, nullptr, stream);
+}
+// Fused step = pass 1 + ONE combined launch: the first blocks take the (few) lifting envs, densely packed,
+// and run lift + action substeps back to back; the other blocks take everybody else. In the lockstep
+// kernel a single lifting env would otherwise hold its whole block for 3S substeps.
 int gmj_step(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, float* obs_dev, float* reward_dev,
              uint8_t* done_dev, float* events_dev, void* stream) {
   if (!h || !actions_dev) FAIL("gmj_step: null handle or actions");
-  return launch_step(h, STEP_SET_ACTION | STEP_SUBSTEPS | STEP_SENSORS | STEP_TAIL | STEP_OUTPUT, -1, actions_dev, frac_dev,
+  if (launch_collect(h, actions_dev, frac_dev, stream)) return 1;
+  return launch_step(h, STEP_SUBSTEPS | STEP_SENSORS | STEP_TAIL | STEP_OUTPUT | STEP_COMBINED, -1, nullptr, nullptr,
                      obs_dev, reward_dev, done_dev, events_dev, stream);
 }
 int gmj_set_action(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, void* stream) {
   if (!h || !actions_dev) FAIL("gmj_set_action: null handle or actions");
-  // the termination action burns 2 x sim_steps_per_action substeps inside set_action (quirk Q8)
-  return launch_step(h, STEP_SET_ACTION | STEP_SUBSTEPS | STEP_SENSORS, 0, actions_dev, frac_dev, nullptr, nullptr, nullptr, nullptr, stream);
+  if (launch_collect(h, actions_dev, frac_dev, stream)) return 1;
+  return launch_step(h, STEP_SUBSTEPS | STEP_SENSORS | STEP_LIST, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, stream);
 }
 int gmj_action_step(GmjHandle* h, void* stream) {
   if (!h) FAIL("null handle");

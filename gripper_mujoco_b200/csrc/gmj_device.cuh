@@ -47,7 +47,7 @@ struct EnvState {
   int weld_on, old_moving, nrow_prev, last_done;
   uint32_t rng_ctr, env_id, episode, obj_index;
   unsigned long long st_contacts, st_rows, st_iters, st_substeps;
-  unsigned int st_unstable, st_overflow, pad0, pad1;
+  unsigned int st_unstable, st_overflow, pending_extra, pad1;   // pending_extra: lift substeps owed by set_action
 };
 
 // model constants, lane-major [field][32] so a warp reads each field conflict-free

@@ -165,6 +165,8 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION") == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from gripper_mujoco_b200 import lib as gl
     from gripper_mujoco_b200.mjclass import MjClass
@@ -247,6 +249,10 @@ def main():
     rew_h = torch.empty(n, dtype=torch.float32).pin_memory()
     done_h = torch.empty(n, dtype=torch.uint8).pin_memory()
     a_dev = torch.empty(n, dtype=torch.int32, device=dev)
+    gatherer = None
+    if world > 1:          # the path's only exchange: transitions of every shard to the learner rank (NCCL gather)
+        from gripper_mujoco_b200.sharding import TransitionGather, shard_range
+        gatherer = TransitionGather(shard_range(world * n, rank, world), gb.n_obs, dev, dst=0)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -255,6 +261,8 @@ def main():
     for k in range(K):
         a_dev.copy_(actions_host[K + W + k], non_blocking=True)
         obs, rew, done = env_step(a_dev)
+        if gatherer is not None:
+            gatherer.gather(obs, rew, done)
         obs_h.copy_(obs, non_blocking=True); rew_h.copy_(rew, non_blocking=True); done_h.copy_(done, non_blocking=True)
         torch.cuda.current_stream().synchronize()      # the learner consumes the transition on the host
     e1.record(); torch.cuda.synchronize()

@@ -11,6 +11,16 @@
 
 // environments (warps) per block of the FP32 step kernel, one block per SM: as many as shared memory
 // holds (N = 5: 12 x 16.1 KB, 14 measured no faster, N = 8: 12 x 18.8 KB of the 227 KB)
+// envs are dealt to blocks in order of expected load so that the warps of a lockstep block finish each
+// phase together (ncu: stall_barrier was the top stall with arrival order)
+#ifndef GMJ_LIFT_WPB
+#define GMJ_LIFT_WPB 12
+#endif
+#define GMJ_SORT_BUCKETS 16
+#define GMJ_SORT_DIV 3
+#ifndef GMJ_BLOCKS_PER_SM
+#define GMJ_BLOCKS_PER_SM 1
+#endif
 #ifndef GMJ_WPB_F32_N5
 #define GMJ_WPB_F32_N5 12
 #endif
@@ -41,11 +51,12 @@ template <typename T> __device__ __forceinline__ void copy_words(void* dst, cons
 template <typename T, int N> struct StepCfg { static constexpr int WPB = sizeof(T) == 4 ? (N <= 5 ? GMJ_WPB_F32_N5 : GMJ_WPB_F32_N8) : 4; };
 
 template <typename T, int N>
-__global__ void __launch_bounds__(32 * StepCfg<T, N>::WPB, 1)
+__global__ void __launch_bounds__(32 * StepCfg<T, N>::WPB, GMJ_BLOCKS_PER_SM)
 k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const DevSettings* __restrict__ Sp, int n_envs,
        int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
        float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,
-       int* __restrict__ err_flag, int* __restrict__ env_list, int* __restrict__ env_count, int list_blocks) {
+       int* __restrict__ err_flag, int* __restrict__ env_list, int* __restrict__ env_count, int list_blocks,
+       const int* __restrict__ perm, int* __restrict__ hist) {
   constexpr int WPB = StepCfg<T, N>::WPB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_nsub_max;
@@ -55,12 +66,21 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
   if (flags & STEP_COMBINED) { list_block = bid < list_blocks; if (!list_block) bid -= list_blocks; }
   int env = bid * WPB + warp;
   bool valid = env < n_envs;
-  if (list_block) {                        // dense blocks over the collected envs; surplus blocks leave at once
+  if (list_block) {                        // the collected envs, GMJ_LIFT_WPB per block; surplus blocks leave at once
+    // a lifting env runs 3S substeps back to back: few warps per block keep that critical path short
+    // (a 4-warp block steps ~2.5x faster than a full one), the idle warps only pass the barriers
+    constexpr int LW = GMJ_LIFT_WPB < WPB ? GMJ_LIFT_WPB : WPB;
     const int cnt = *env_count;
-    if (bid * WPB >= cnt) return;
-    valid = env < cnt;
+    if (bid * LW >= cnt) return;
+    env = bid * LW + warp;
+    valid = warp < LW && env < cnt;
     env = valid ? env_list[env] : 0;
-  } else if ((flags & STEP_COMBINED) && valid) valid = envs[env].pending_extra == 0;
+  } else if (flags & STEP_COMBINED) {      // everybody else, in the load-sorted order built by k_sort_scatter
+    const int n_rest = n_envs - *env_count;
+    if (bid * WPB >= n_rest) return;
+    valid = env < n_rest;
+    env = valid ? perm[env] : 0;
+  }
   WarpShared<T, N>& ws = *reinterpret_cast<WarpShared<T, N>*>(smem_raw + (size_t)warp * sizeof(WarpShared<T, N>));
   const DevModel<T>& M = *Mp; const DevSettings& S = *Sp;
   if (threadIdx.x == 0) s_nsub_max = 0;
@@ -80,6 +100,10 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
     if ((flags & STEP_COLLECT) && lane == 0) {
       e.pending_extra = extra;
       if (extra > 0) env_list[atomicAdd(env_count, 1)] = env;
+      else {                               // load key: constraint rows of the last substep (contacts dominate the cost)
+        int key = e.nrow_prev / GMJ_SORT_DIV; if (key >= GMJ_SORT_BUCKETS) key = GMJ_SORT_BUCKETS - 1;
+        e.sort_key = key; atomicAdd(&hist[key], 1);
+      }
     }
     extra = __shfl_sync(GMJ_FULL, extra, 0);
     __syncwarp();
@@ -128,6 +152,19 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
   }
   __syncwarp();
   copy_words<T>(&envs[env], &ws.e, sizeof(EnvState<T>), lane);
+}
+
+// counting-sort scatter of the envs that owe no lift substeps: perm[offset(key) + slot] = env
+template <typename T>
+__global__ void k_sort_scatter(const EnvState<T>* __restrict__ envs, int n_envs, const int* __restrict__ hist,
+                               int* __restrict__ cursor, int* __restrict__ perm) {
+  int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= n_envs) return;
+  if (envs[env].pending_extra > 0) return;
+  const int key = (int)envs[env].sort_key;
+  int off = 0;
+  for (int k = GMJ_SORT_BUCKETS - 1; k > key; k--) off += hist[k];      // heaviest first
+  perm[off + atomicAdd(&cursor[key], 1)] = env;
 }
 
 // MjClass::reset + luke::reset (src/mjclass.cpp:434-486, src/myfunctions.cpp:544-570): one thread per env
@@ -329,6 +366,7 @@ struct GmjHandle {
   GmjObject* objects; int n_objects;
   int* err_flag;
   int* env_list; int* env_count;   // envs that owe the 2S termination-lift substeps this step
+  int* perm; int* hist;            // load-sorted order of the other envs; hist[0..16) counts, hist[16..32) cursors
   unsigned long long* stats_dev;
   double* scratch; size_t scratch_len;
   GmjModel hm;
@@ -459,9 +497,11 @@ static int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* acti
   static bool attr_set = false;
   if (!attr_set) { CK(cudaFuncSetAttribute(k_step<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
   int blocks = (h->n_envs + WPB - 1) / WPB;
-  const int list_blocks = combined ? blocks : 0;      // worst case every env owes a lift; empty list blocks exit at once
+  constexpr int LW = GMJ_LIFT_WPB < WPB ? GMJ_LIFT_WPB : WPB;
+  if (flags & STEP_LIST) blocks = (h->n_envs + LW - 1) / LW;
+  const int list_blocks = combined ? (h->n_envs + LW - 1) / LW : 0;   // worst case every env owes a lift; empty list blocks exit at once
   k_step<T, N><<<blocks + list_blocks, 32 * WPB, smem, st>>>((EnvState<T>*)h->envs, (const DevModel<T>*)h->model, h->settings,
-      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks);
+      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks, h->perm, h->hist);
   CK(cudaGetLastError());
   h->smem_bytes = smem;
   return 0;
@@ -527,6 +567,7 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
   CK(cudaMalloc(&h->stats_dev, 8 * sizeof(unsigned long long)));
   CK(cudaMalloc(&h->env_list, sizeof(int) * (size_t)n_envs)); CK(cudaMalloc(&h->env_count, sizeof(int)));
   CK(cudaMemset(h->env_count, 0, sizeof(int)));
+  CK(cudaMalloc(&h->perm, sizeof(int) * (size_t)n_envs)); CK(cudaMalloc(&h->hist, sizeof(int) * 2 * GMJ_SORT_BUCKETS));
   if (gmj_set_settings(h, settings)) { return 1; }
   *out = h;
   return gmj_reset(h, nullptr, nullptr);
@@ -535,7 +576,7 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
 int gmj_destroy(GmjHandle* h) {
   if (!h) return 0;
   cudaSetDevice(h->device);
-  cudaFree(h->envs); cudaFree(h->model); cudaFree(h->settings); cudaFree(h->err_flag); cudaFree(h->stats_dev); cudaFree(h->env_list); cudaFree(h->env_count);
+  cudaFree(h->envs); cudaFree(h->model); cudaFree(h->settings); cudaFree(h->err_flag); cudaFree(h->stats_dev); cudaFree(h->env_list); cudaFree(h->env_count); cudaFree(h->perm); cudaFree(h->hist);
   if (h->objects) cudaFree(h->objects);
   if (h->scratch) cudaFree(h->scratch);
   delete h;
@@ -585,7 +626,13 @@ int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const 
 static int launch_collect(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, void* stream) {
   CK(cudaSetDevice(h->device));
   CK(cudaMemsetAsync(h->env_count, 0, sizeof(int), (cudaStream_t)stream));
-  return launch_step(h, STEP_SET_ACTION | STEP_COLLECT, 0, actions_dev, frac_dev, nullptr, nullptr, nullptr, nullptr, stream);
+  CK(cudaMemsetAsync(h->hist, 0, sizeof(int) * 2 * GMJ_SORT_BUCKETS, (cudaStream_t)stream));
+  if (launch_step(h, STEP_SET_ACTION | STEP_COLLECT, 0, actions_dev, frac_dev, nullptr, nullptr, nullptr, nullptr, stream)) return 1;
+  int tb = 256, nb = (h->n_envs + tb - 1) / tb;
+  if (h->precision == 0) k_sort_scatter<float><<<nb, tb, 0, (cudaStream_t)stream>>>((const EnvState<float>*)h->envs, h->n_envs, h->hist, h->hist + GMJ_SORT_BUCKETS, h->perm);
+  else k_sort_scatter<double><<<nb, tb, 0, (cudaStream_t)stream>>>((const EnvState<double>*)h->envs, h->n_envs, h->hist, h->hist + GMJ_SORT_BUCKETS, h->perm);
+  CK(cudaGetLastError());
+  return 0;
 }
 // Fused step = pass 1 + ONE combined launch: the first blocks take the (few) lifting envs, densely packed,
 // and run lift + action substeps back to back; the other blocks take everybody else. In the lockstep

@@ -47,7 +47,7 @@ struct EnvState {
   int weld_on, old_moving, nrow_prev, last_done;
   uint32_t rng_ctr, env_id, episode, obj_index;
   unsigned long long st_contacts, st_rows, st_iters, st_substeps;
-  unsigned int st_unstable, st_overflow, pending_extra, pad1;   // pending_extra: lift substeps owed by set_action
+  unsigned int st_unstable, st_overflow, pending_extra, sort_key;   // pending_extra: lift substeps owed by set_action
 };
 
 // model constants, lane-major [field][32] so a warp reads each field conflict-free
@@ -139,11 +139,24 @@ template <typename T> __device__ __forceinline__ M3<T> quat2mat(T w, T x, T y, T
 template <typename T> __device__ __forceinline__ void sincosT(T t, T* s, T* c);
 template <> __device__ __forceinline__ void sincosT<float>(float t, float* s, float* c) { sincosf(t, s, c); }
 template <> __device__ __forceinline__ void sincosT<double>(double t, double* s, double* c) { sincos(t, s, c); }
+
+// Double-precision libm calls expand to hundreds of SASS instructions each; the step kernel runs at
+// the speed of instruction fetch, so every call site shares ONE out-of-line copy.
+__device__ __noinline__ double nd_asin(double x) { return asin(x); }
+__device__ __noinline__ double nd_sin(double x) { return sin(x); }
+__device__ __noinline__ double nd_cos(double x) { return cos(x); }
+__device__ __noinline__ double nd_round(double x) { return round(x); }
+__device__ __noinline__ double nd_log(double x) { return log(x); }
 template <typename T> __device__ __forceinline__ T sqrtT(T x);
-template <> __device__ __forceinline__ float sqrtT<float>(float x) { return sqrtf(x); }
+template <> __device__ __forceinline__ float sqrtT<float>(float x) {
+  // MUFU.RSQ + one Newton step (<= 1 ulp), no out-of-line slow path: sqrtf() is ~12 instructions per site
+  float r = rsqrtf(x), s0 = x * r;
+  s0 = fmaf(fmaf(-s0, s0, x), 0.5f * r, s0);
+  return x > 0.0f ? s0 : 0.0f;
+}
 template <> __device__ __forceinline__ double sqrtT<double>(double x) { return sqrt(x); }
 template <typename T> __device__ __forceinline__ T rsqrtT(T x);
-template <> __device__ __forceinline__ float rsqrtT<float>(float x) { return 1.0f / sqrtf(x); }
+template <> __device__ __forceinline__ float rsqrtT<float>(float x) { float r = rsqrtf(x); return r * fmaf(fmaf(-x * r, r, 1.0f), 0.5f, 1.0f); }
 template <> __device__ __forceinline__ double rsqrtT<double>(double x) { return 1.0 / sqrt(x); }
 template <typename T> __device__ __forceinline__ T absT(T x) { return x < 0 ? -x : x; }
 template <typename T> __device__ __forceinline__ T maxT(T a, T b) { return a > b ? a : b; }

@@ -150,8 +150,11 @@ template <typename T> __device__ __forceinline__ T impedance(const T* solimp, T 
   if (x >= 1) return dw;
   if (x <= 0) return d0;
   T y;
-  if (x <= mid) y = powT<T>(x / mid, power) * mid;
-  else y = 1 - powT<T>((1 - x) / (1 - mid), power) * (1 - mid);
+  // power = 2 in every model of the reference (solimp "0.9 0.95 0.001 0.5 2"): no powf expansion on the hot path
+  T a = (x <= mid) ? x / mid : (1 - x) / (1 - mid);
+  T ap = (power == T(2)) ? a * a : powT<T>(a, power);
+  if (x <= mid) y = ap * mid;
+  else y = 1 - ap * (1 - mid);
   return d0 + y * (dw - d0);
 }
 

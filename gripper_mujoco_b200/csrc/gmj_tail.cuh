@@ -31,8 +31,8 @@ struct WarpAux {                 // per-warp scratch written by the physics each
 #define G_XY_HOME (G_XY_MAX - 1.0 * (4 * 1e-3 / 1.0))
 #define G_Z_HOME (0.0 + 1.0 * (4.8768 * 1e-3 / 1))
 
-__device__ __forceinline__ double g_calc_th(double x, double y) { return asin((y - x) / G_LEADSCREW); }
-__device__ __forceinline__ double g_calc_y(double x, double th) { return x + G_LEADSCREW * sin(th); }
+__device__ __forceinline__ double g_calc_th(double x, double y) { return nd_asin((y - x) / G_LEADSCREW); }
+__device__ __forceinline__ double g_calc_y(double x, double th) { return x + G_LEADSCREW * nd_sin(th); }
 
 __device__ inline int g_update_xy(DevGripper& g) {                    // gripper.cpp:6-90
   int wl = 1;
@@ -47,17 +47,22 @@ __device__ inline int g_update_xy(DevGripper& g) {                    // gripper
   if (nth < th_min) { nth = th_min; g.y = g_calc_y(g.x, th_min); wl = 0; }
   g.th = nth;
   const double hyp = sqrt(235e-3 * 235e-3 + 35.0e-3 * 35.0e-3), rest = atan(35.0e-3 / 235e-3);
-  double th_lim = asin((-1.0 - g.x) / hyp) + rest;                    // fingertip_radius_min = -1 (disabled)
-  if (g.th < th_lim) { g.y = g_calc_y(g.x, th_lim); g.th = th_lim; wl = 0; }
-  g.sx = (int)round((G_XY_MAX - g.x) / G_XY_STEP);
-  g.sy = (int)round((G_XY_MAX - g.y) / G_XY_STEP);
+  // fingertip_radius_min = -1 (disabled): the asin argument is below -1 for every reachable x, the
+  // reference gets NaN and the comparison is false; the call is only made when it can matter
+  const double targ = (-1.0 - g.x) / hyp;
+  if (targ >= -1.0 && targ <= 1.0) {
+    double th_lim = nd_asin(targ) + rest;
+    if (g.th < th_lim) { g.y = g_calc_y(g.x, th_lim); g.th = th_lim; wl = 0; }
+  }
+  g.sx = (int)nd_round((G_XY_MAX - g.x) / G_XY_STEP);
+  g.sy = (int)nd_round((G_XY_MAX - g.y) / G_XY_STEP);
   return wl;
 }
 __device__ inline int g_update_z(DevGripper& g) {                     // gripper.cpp:92-118
   int wl = 1;
   if (g.z > G_Z_MAX + G_LIMIT_TOL) { g.z = G_Z_MAX; wl = 0; }
   if (g.z < 0.0 - G_LIMIT_TOL) { g.z = 0.0; wl = 0; }
-  g.sz = (int)round(g.z / G_Z_STEP);
+  g.sz = (int)nd_round(g.z / G_Z_STEP);
   return wl;
 }
 __device__ inline int g_set_xyz_m(DevGripper& g, double x, double y, double z) {
@@ -136,7 +141,7 @@ __device__ inline int sample_stream(const EnvState<T>& e, int st, int mode, int 
 }
 
 // ------------------------------------------------------------------ sensors
-template <typename T> __device__ inline float dev_uniform(EnvState<T>& e, const DevSettings& S) {
+template <typename T> __device__ __noinline__ float dev_uniform(EnvState<T>& e, const DevSettings& S) {
   uint64_t seed = (uint64_t)S.s.general[GS_random_seed];
   uint32_t x = philox_first(e.rng_ctr++, e.env_id, 0, 0, (uint32_t)seed, (uint32_t)(seed >> 32));
   return (float)(x >> 8) * (1.0f / 16777216.0f);
@@ -163,8 +168,8 @@ __device__ inline float apply_noise(EnvState<T>& e, const DevSettings& S, int se
     float u1, u2;
     do { u1 = dev_uniform(e, S); } while (u1 <= eps);
     u2 = dev_uniform(e, S);
-    float mag = (float)(noise_std * sqrt(-2.0 * log((double)u1)));
-    float z0 = (float)(mag * cos((double)(6.2831853071795864769f * u2))) + mu;
+    float mag = (float)(noise_std * sqrt(-2.0 * nd_log((double)u1)));
+    float z0 = (float)(mag * nd_cos((double)(6.2831853071795864769f * u2))) + mu;
     value += z0;
   }
   if (value > 1) value = 1; else if (value < -1) value = -1;
@@ -186,8 +191,8 @@ __device__ inline float read_gauge(const EnvState<T>& e, const DevModel<T>& M, i
   double cum = 0; fx[0] = 0; y[0] = 0;
   for (int i = 0; i < N; i++) {
     cum += (double)e.qpos[3 + finger * (N + 2) + i];
-    fx[i + 1] = fx[i] + L * cos(cum);
-    y[i + 1] = y[i] + L * sin(cum);
+    fx[i + 1] = fx[i] + L * nd_cos(cum);
+    y[i + 1] = y[i] + L * nd_sin(cum);
   }
   const int n = N + 1;
   for (int i = 0; i < n; i++) { X[i][0] = fx[i] * fx[i] * fx[i]; X[i][1] = fx[i] * fx[i]; X[i][2] = fx[i]; X[i][3] = 1; }
@@ -421,7 +426,7 @@ __device__ inline int set_action(EnvState<T>& e, const DevSettings& S, const Dev
   }
   {  // luke::get_fingertip_z_height (src/myfunctions.cpp:3608-3620)
     float straight = (float)(-g[GS_base_z_min] - e.base_z);
-    float tip_lift = (float)((double)M.finger_length * (1 - cos(g_calc_th(e.tend.x, e.tend.y))));
+    float tip_lift = (float)((double)M.finger_length * (1 - nd_cos(g_calc_th(e.tend.x, e.tend.y))));
     float above = straight + tip_lift;
     float h = (float)((double)above + g[GS_base_z_min]);
     if (h < g[GS_fingertip_min_mm] * 1e-3) wl = 0;
@@ -461,16 +466,16 @@ __device__ inline void sense_gripper_state(EnvState<T>& e, const DevSettings& S,
   double fing_x = e.tend.x, fing_th = g_calc_th(e.tend.x, e.tend.y), palm_z = e.tend.z;
   double L = (double)M.finger_length;
   double untilted = (double)M.clearance - e.base_z;
-  double tilted = untilted + L * (1 - cos(fing_th));
+  double tilted = untilted + L * (1 - nd_cos(fing_th));
   const double ft = 0.2, PI_23 = 3.14159265358979323846 * (2.0 / 3.0);
   for (int i = 0; i < 3; i++) {
     double ang = i * PI_23;
-    double tilt_x = fing_x - L * sin(fing_th);
+    double tilt_x = fing_x - L * nd_sin(fing_th);
     double defl = Fg[i] * (L * L * L) / (3 * (double)M.EI);
-    double fx = tilt_x + defl * cos(fing_th);
-    double px = -fx * sin(ang + e.base_yaw) + e.base_x;
-    double py = -fx * cos(ang + e.base_yaw) + e.base_y;
-    double pz = tilted - defl * sin(fing_th);
+    double fx = tilt_x + defl * nd_cos(fing_th);
+    double px = -fx * nd_sin(ang + e.base_yaw) + e.base_x;
+    double py = -fx * nd_cos(ang + e.base_yaw) + e.base_y;
+    double pz = tilted - defl * nd_sin(fing_th);
     int on = fabs(Fg[i]) > ft;
     win_add(e, ST_cart + 3 * i + 0, on ? (float)px : 0.0f);
     win_add(e, ST_cart + 3 * i + 1, on ? (float)py : 0.0f);

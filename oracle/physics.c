@@ -194,8 +194,11 @@ static double impedance(const double* solimp, double pos) {
   if (x >= 1) return dw;
   if (x <= 0) return d0;
   double y;
-  if (x <= mid) y = pow(x / mid, power) * mid;     /* a*x^p with a = 1/mid^(p-1) */
-  else y = 1 - pow((1 - x) / (1 - mid), power) * (1 - mid);
+  /* a*x^p with a = 1/mid^(p-1); p = 2 in every reference model: squared explicitly, as the device does */
+  double a = (x <= mid) ? x / mid : (1 - x) / (1 - mid);
+  double ap = (power == 2.0) ? a * a : pow(a, power);
+  if (x <= mid) y = ap * mid;
+  else y = 1 - ap * (1 - mid);
   return d0 + y * (dw - d0);
 }
 

@@ -194,18 +194,28 @@ def test_full_size_properties():
 
 def test_calibration_matches_oracle_fp64():
     """configure_settings auto-calibration (reset pose, timestep search, sim steps, wrist-Z offset,
-    gauge normalisation) over the FP64 CUDA kernels == the same flow over the oracle."""
+    gauge normalisation) over the FP64 CUDA kernels vs the same flow over the oracle. The stability
+    edge of the timestep search is chaotic (1 ulp decides whether a 1 s run at the edge blows up), so it
+    is compared to within two 50 us search increments; the sensor calibration is then compared at the SAME
+    timestep, tightly."""
+    from gripper_mujoco_b200 import calibration
     from gripper_mujoco_b200.mjclass import MjClass
     from gripper_mujoco_b200.model import GripperParams
-    from oracle.calibrate import calibrated
-    mj = MjClass(2, GripperParams(num_segments=5), precision="fp64")
-    _, s, info = calibrated(GripperParams(num_segments=5))
+    from oracle.calibrate import calibrated, make_backend
+    p = GripperParams(num_segments=5)
+    mj = MjClass(2, p, precision="fp64")
+    mdl, s, info = calibrated(p)
     g = mj.set
-    assert g.mujoco_timestep == s.mujoco_timestep and g.sim_steps_per_action == s.sim_steps_per_action
-    assert mj.highest_stable_timestep == info["highest_stable_timestep"]
+    assert abs(mj.highest_stable_timestep - info["highest_stable_timestep"]) <= 1.01e-4
+    assert abs(g.sim_steps_per_action - s.sim_steps_per_action) <= 1
+    assert g.sim_steps_per_action == int(np.ceil(g.time_for_action / g.mujoco_timestep))
     assert abs(g.reset_qpos_base - s.reset_qpos_base) < 1e-10 and abs(g.reset_qpos_g6 - s.reset_qpos_g6) < 1e-10
-    assert abs(g.wrist_sensor_Z.raw_value_offset - s.wrist_sensor_Z.raw_value_offset) < 1e-5
-    assert abs(g.bending_gauge.normalise / s.bending_gauge.normalise - 1) < 1e-5
+    s2 = s.copy()
+    s2.mujoco_timestep = g.mujoco_timestep
+    calibration.calibrate_simulated_sensors(s2, float(np.float32(s2.saturation_yield_factor * calibration.yield_load(p))),
+                                            make_backend(mdl))
+    assert abs(g.wrist_sensor_Z.raw_value_offset - s2.wrist_sensor_Z.raw_value_offset) < 1e-5
+    assert abs(g.bending_gauge.normalise / s2.bending_gauge.normalise - 1) < 1e-6
     mj.close()
 
 

@@ -129,6 +129,32 @@ __device__ __forceinline__ T ldl_fwd(const Topo<N>& tp, const T* Lrow, T lb, T x
   if (tp.lane == 0) x -= s;
   return x;
 }
+// K right-hand sides at once: the chain recursion is latency bound (one shuffle + FMA per level), so
+// independent columns ride along for free
+template <typename T, int N, int K>
+__device__ __forceinline__ void ldl_fwdK(const Topo<N>& tp, const T* Lrow, T lb, T (&x)[K]) {
+  constexpr int NL = N + 2;
+#pragma unroll
+  for (int k = 0; k < NL - 1; k++) {
+#pragma unroll
+    for (int m = 0; m < K; m++) {
+      T xk = __shfl_sync(GMJ_FULL, x[m], tp.fb + k);
+      if (tp.chain && tp.local > k) x[m] -= Lrow[k] * xk;
+    }
+  }
+  T sv[K];
+#pragma unroll
+  for (int m = 0; m < K; m++) sv[m] = (tp.lane != 0 && tp.act) ? lb * x[m] : T(0);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int m = 0; m < K; m++) sv[m] += __shfl_xor_sync(GMJ_FULL, sv[m], o);
+  }
+  if (tp.lane == 0) {
+#pragma unroll
+    for (int m = 0; m < K; m++) x[m] -= sv[m];
+  }
+}
 // y = L x
 template <typename T, int N>
 __device__ __forceinline__ T ldl_mulL(const Topo<N>& tp, const T* Lrow, T lb, T x) {
@@ -173,6 +199,18 @@ __device__ __forceinline__ void emit_row(WarpShared<T, N>& ws, const Topo<N>& tp
   }
 }
 
+// store an already whitened row (lane value xw) + meta
+template <typename T, int N>
+__device__ __forceinline__ void put_row(WarpShared<T, N>& ws, const Topo<N>& tp, const T* rsqo, int r, T xw,
+                                        const T* Jo, int type, T pos, T jv, T mu, int first, int jl) {
+  if (tp.act) ws.W[r][tp.lane] = xw;
+  if (tp.lane == 0) {
+#pragma unroll
+    for (int k = 0; k < 6; k++) ws.W[r][3 * N + 8 + k] = Jo[k] * rsqo[k];
+    ws.rtype[r] = type; ws.rpos[r] = pos; ws.rjv[r] = jv; ws.rmu[r] = mu; ws.rfirst[r] = first; ws.rlane[r] = jl;
+  }
+}
+
 // point Jacobian entry of this lane's dof for a point p on gripper body `bl` (lane index) projected
 // on direction d: d . (a x (p - anchor)) for hinges, d . a for slides, 0 if the dof is not an ancestor
 template <typename T, int N>
@@ -188,34 +226,43 @@ __device__ __forceinline__ T jac_entry(const Topo<N>& tp, int bl, V3<T> p, V3<T>
 
 
 // ------------------------------------------------------------------ A = W W^T, packed lower triangle
-// Lane owns rows lane and lane + 32 and computes columns cc <= row. bcol (optional) = W_r . W[nr] (the
-// whitened smooth force), the extra column of the dual.
+// Entry-parallel: the nr (nr + 1) / 2 packed entries are dealt 32 at a time, lane e computes
+// A[i][j] = W_i . W_j for its entry (W_i is a broadcast or near-broadcast read, W_j walks rows with an odd
+// stride). bcol (optional, per owned row lane / lane + 32) = W_r . W[nr], the extra column of the dual.
 template <typename T, int N>
 __device__ void form_A(WarpShared<T, N>& ws, int nr, int lane, T* bcol) {
   constexpr int NW = WarpShared<T, N>::NW;
+  const int ne = nr * (nr + 1) / 2;
 #pragma unroll 1
-  for (int slot = 0; slot < 2; slot++) {
-    const int r = lane + 32 * slot;
-    if (bcol) bcol[slot] = 0;
-    if (slot == 1 && nr <= 32) break;
-    const bool own = r < nr;
-    T wr[NW];
+  for (int e0 = 0; e0 < ne; e0 += 32) {
+    const int e = e0 + lane;
+    const bool ok = e < ne;
+    const int ee = ok ? e : 0;
+    int i = (int)((sqrtf(8.0f * (float)ee + 1.0f) - 1.0f) * 0.5f);
+    if ((i + 1) * (i + 2) / 2 <= ee) i++;
+    if (i * (i + 1) / 2 > ee) i--;
+    const int j = ee - i * (i + 1) / 2;
+    const T* wi = ws.W[i];
+    const T* wj = ws.W[j];
+    T a0 = 0, a1 = 0;
 #pragma unroll
-    for (int k = 0; k < NW; k++) wr[k] = own ? ws.W[r][k] : T(0);
-    const int top = nr - 1 < 31 + 32 * slot ? nr - 1 : 31 + 32 * slot;     // largest owned row of this slot in the warp
-    for (int cc = 0; cc <= top; cc++) {
+    for (int k = 0; k + 1 < NW; k += 2) { a0 += wi[k] * wj[k]; a1 += wi[k + 1] * wj[k + 1]; }
+    if (NW & 1) a0 += wi[NW - 1] * wj[NW - 1];
+    if (ok) ws.A[ee] = a0 + a1;
+  }
+  if (bcol) {
+#pragma unroll 1
+    for (int slot = 0; slot < 2; slot++) {
+      const int r = lane + 32 * slot;
+      bcol[slot] = 0;
+      if (slot == 1 && nr <= 32) break;
+      const T* wr = ws.W[r < nr ? r : 0];
+      const T* wn = ws.W[nr];
       T a0 = 0, a1 = 0;
 #pragma unroll
-      for (int k = 0; k + 1 < NW; k += 2) { a0 += wr[k] * ws.W[cc][k]; a1 += wr[k + 1] * ws.W[cc][k + 1]; }
-      if (NW & 1) a0 += wr[NW - 1] * ws.W[cc][NW - 1];
-      if (own && cc <= r) ws.A[TRI(r, cc)] = a0 + a1;
-    }
-    if (bcol) {
-      T a0 = 0, a1 = 0;
-#pragma unroll
-      for (int k = 0; k + 1 < NW; k += 2) { a0 += wr[k] * ws.W[nr][k]; a1 += wr[k + 1] * ws.W[nr][k + 1]; }
-      if (NW & 1) a0 += wr[NW - 1] * ws.W[nr][NW - 1];
-      bcol[slot] = a0 + a1;
+      for (int k = 0; k + 1 < NW; k += 2) { a0 += wr[k] * wn[k]; a1 += wr[k + 1] * wn[k + 1]; }
+      if (NW & 1) a0 += wr[NW - 1] * wn[NW - 1];
+      bcol[slot] = r < nr ? a0 + a1 : T(0);
     }
   }
 }
@@ -245,36 +292,37 @@ __device__ int lcp_solve(WarpShared<T, N>& ws, int nr, int lane, const T* b, con
     if (it > 0) { __syncwarp(); form_A<T, N>(ws, nr, lane, nullptr); __syncwarp(); }
     it++;
     const unsigned m0 = __ballot_sync(GMJ_FULL, act0), m1 = __ballot_sync(GMJ_FULL, act1);
-    // ---- left-looking Cholesky of K_FF (identity on the inactive rows), column j
+    // ---- left-looking Cholesky of K_FF (identity on the inactive rows), column j. The rows below the
+    // diagonal are dealt to the lanes afresh for every column (row j + lane), so a second pass is only
+    // needed while more than 32 rows remain -- not for every column of a system with more than 32 rows.
     T ld0 = 1, ld1 = 1;                       // 1 / L[r][r] of the owned rows
     const int t0 = TRI(r0, 0), t1 = TRI(r1, 0);
     for (int j = 0; j < nr; j++) {
       const bool jact = j < 32 ? ((m0 >> j) & 1) : ((m1 >> (j - 32)) & 1);
       const int tj = TRI(j, 0);
-      T s0 = 0, s1 = 0;
-      if (jact) {
-        if (act0 && r0 >= j) {
-          T a = A[t0 + j], c = 0;
+      const T Rj = __shfl_sync(GMJ_FULL, j < 32 ? R[0] : R[1], j & 31);
+      T inv = 1;
+#pragma unroll 1
+      for (int base = j; base < nr; base += 32) {
+        const int i = base + lane;
+        const bool iact = i < nr && ((i < 32 ? (m0 >> i) : (m1 >> (i - 32))) & 1);
+        const int ti = TRI(i, 0);
+        T sv = 0;
+        if (jact && iact) {
+          T a = A[ti + j], c = 0;
           int k = 0;
-          for (; k + 1 < j; k += 2) { a -= A[t0 + k] * A[tj + k]; c -= A[t0 + k + 1] * A[tj + k + 1]; }
-          if (k < j) a -= A[t0 + k] * A[tj + k];
-          s0 = a + c + (r0 == j ? R[0] : T(0));
+          for (; k + 1 < j; k += 2) { a -= A[ti + k] * A[tj + k]; c -= A[ti + k + 1] * A[tj + k + 1]; }
+          if (k < j) a -= A[ti + k] * A[tj + k];
+          sv = a + c + (i == j ? Rj : T(0));
         }
-        if (two && act1 && r1 >= j) {
-          T a = A[t1 + j], c = 0;
-          int k = 0;
-          for (; k + 1 < j; k += 2) { a -= A[t1 + k] * A[tj + k]; c -= A[t1 + k + 1] * A[tj + k + 1]; }
-          if (k < j) a -= A[t1 + k] * A[tj + k];
-          s1 = a + c + (r1 == j ? R[1] : T(0));
+        if (base == j) {
+          const T dj = __shfl_sync(GMJ_FULL, sv, 0);
+          inv = jact ? rsqrtT<T>(maxT<T>(dj, T(1e-30))) : T(1);
         }
+        if (i > j && i < nr) A[ti + j] = sv * inv;
       }
-      T dj = __shfl_sync(GMJ_FULL, j < 32 ? s0 : s1, j & 31);
-      T inv = jact ? rsqrtT<T>(maxT<T>(dj, T(1e-30))) : T(1);
       if (r0 == j) ld0 = inv;
       if (r1 == j) ld1 = inv;
-      __syncwarp();
-      if (r0 > j && r0 < nr) A[t0 + j] = s0 * inv;
-      if (two && r1 > j && r1 < nr) A[t1 + j] = s1 * inv;
       __syncwarp();
     }
     // ---- forward substitution L y = -b_F
@@ -645,26 +693,45 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   phase_barrier<NT>(5);
   int nr = 0;
   const T zero6[6] = { 0, 0, 0, 0, 0, 0 };
+  // Welds and joint limits act on ONE joint each: every such row is a multiple of L^-1 e_j, so the unit
+  // solves are done four joints at a time and the rows are scaled copies.
   // welds: joint `j` locked at its anchor; rows = world components of the joint axis
   // (weld residual of MuJoCo restricted to the single joint between the two bodies)
+  {
+    const unsigned won = e.weld_on & 0x7f;
 #pragma unroll 1
-  for (int id = 0; id < 7; id++) {
-    if (!((e.weld_on >> id) & 1)) continue;
-    int j = (id < 3) ? (1 + id * NL) : ((id < 6) ? (2 + (id - 3) * NL) : PALM);
-    V3<T> aj = shfl3(aw, j);
-    T qj = __shfl_sync(GMJ_FULL, q, j), qdj = __shfl_sync(GMJ_FULL, qd, j);
-    bool rev = (id >= 3 && id < 6);
-    T sgn = rev ? T(-1) : T(1);
-    T s1, c1; sincosT<T>(qj - e.weld_anchor[id], &s1, &c1);
-    T rho = rev ? s1 : (qj - e.weld_anchor[id]);
-    T comp[3] = { aj.x, aj.y, aj.z };
+    for (int g = 0; g < 2; g++) {
+      unsigned grp = g == 0 ? (won & 0x0f) : (won >> 4);       // ids 0-3, then 4-6
+      if (!grp) continue;
+      T x[4];
 #pragma unroll
-    for (int d = 0; d < 3; d++) {
-      if (comp[d] * comp[d] < T(1e-10)) continue;
-      if (nr >= GMJ_RMAX) break;
-      T Jl = (lane == j) ? sgn * comp[d] : T(0);
-      emit_row<T, N>(ws, tp, Mrow, lb, rsq, rsqo, nr, Jl, zero6, ROW_EQ, sgn * rho * comp[d], sgn * comp[d] * qdj, T(0), nr, j);
-      nr++;
+      for (int m = 0; m < 4; m++) {
+        const int id = 4 * g + m;
+        const int j = (id < 3) ? (1 + id * NL) : ((id < 6) ? (2 + (id - 3) * NL) : PALM);
+        x[m] = (((grp >> m) & 1) && lane == j) ? T(1) : T(0);
+      }
+      ldl_fwdK<T, N, 4>(tp, Mrow, lb, x);
+#pragma unroll
+      for (int m = 0; m < 4; m++) {
+        const int id = 4 * g + m;
+        if (id > 6 || !((grp >> m) & 1)) continue;
+        const int j = (id < 3) ? (1 + id * NL) : ((id < 6) ? (2 + (id - 3) * NL) : PALM);
+        V3<T> aj = shfl3(aw, j);
+        T qj = __shfl_sync(GMJ_FULL, q, j), qdj = __shfl_sync(GMJ_FULL, qd, j);
+        const bool rev = (id >= 3 && id < 6);
+        const T sgn = rev ? T(-1) : T(1);
+        T s1, c1; sincosT<T>(qj - e.weld_anchor[id], &s1, &c1);
+        const T rho = rev ? s1 : (qj - e.weld_anchor[id]);
+        const T comp[3] = { aj.x, aj.y, aj.z };
+        const T xw = x[m] * rsq;
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+          if (comp[d] * comp[d] < T(1e-10)) continue;
+          if (nr >= GMJ_RMAX) break;
+          put_row<T, N>(ws, tp, rsqo, nr, sgn * comp[d] * xw, zero6, ROW_EQ, sgn * rho * comp[d], sgn * comp[d] * qdj, T(0), nr, j);
+          nr++;
+        }
+      }
     }
   }
   // joint limits (margin 0)
@@ -673,13 +740,27 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
     unsigned mlo = __ballot_sync(GMJ_FULL, tp.act && lo < 0), mhi = __ballot_sync(GMJ_FULL, tp.act && hi < 0);
     unsigned any = mlo | mhi;
     while (any) {
-      int j = __ffs(any) - 1; any &= any - 1;
-      T loj = __shfl_sync(GMJ_FULL, lo, j), hij = __shfl_sync(GMJ_FULL, hi, j), qdj = __shfl_sync(GMJ_FULL, qd, j);
-      if (((mlo >> j) & 1) && nr < GMJ_RMAX) { emit_row<T, N>(ws, tp, Mrow, lb, rsq, rsqo, nr, lane == j ? T(1) : T(0), zero6, ROW_LIMIT, loj, qdj, T(1), nr, j); nr++; }
-      if (((mhi >> j) & 1) && nr < GMJ_RMAX) { emit_row<T, N>(ws, tp, Mrow, lb, rsq, rsqo, nr, lane == j ? T(-1) : T(0), zero6, ROW_LIMIT, hij, -qdj, T(-1), nr, j); nr++; }
+      int jj[4]; T x[4];
+#pragma unroll
+      for (int m = 0; m < 4; m++) {
+        jj[m] = any ? __ffs(any) - 1 : -1;
+        if (any) any &= any - 1;
+        x[m] = (lane == jj[m]) ? T(1) : T(0);
+      }
+      ldl_fwdK<T, N, 4>(tp, Mrow, lb, x);
+#pragma unroll
+      for (int m = 0; m < 4; m++) {
+        const int j = jj[m];
+        if (j < 0) continue;
+        T loj = __shfl_sync(GMJ_FULL, lo, j), hij = __shfl_sync(GMJ_FULL, hi, j), qdj = __shfl_sync(GMJ_FULL, qd, j);
+        const T xw = x[m] * rsq;
+        if (((mlo >> j) & 1) && nr < GMJ_RMAX) { put_row<T, N>(ws, tp, rsqo, nr, xw, zero6, ROW_LIMIT, loj, qdj, T(1), nr, j); nr++; }
+        if (((mhi >> j) & 1) && nr < GMJ_RMAX) { put_row<T, N>(ws, tp, rsqo, nr, -xw, zero6, ROW_LIMIT, hij, -qdj, T(-1), nr, j); nr++; }
+      }
     }
   }
-  // contacts: pyramidal, condim 3 -> 4 rows each
+  // contacts: pyramidal, condim 3 -> 4 rows each, all four linear in the three frame rows (n, t1, t2),
+  // which are whitened together
 #pragma unroll 1
   for (int cidx = 0; cidx < ncon; cidx++) {
     if (nr + 4 > GMJ_RMAX) { ncon = cidx; break; }
@@ -697,7 +778,6 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
       // object part (body2 == B): linear dofs world, angular dofs body frame
 #pragma unroll
       for (int k = 0; k < 6; k++) Joc[ax3][k] = 0;
-      T jvo = 0;
       if (b2 == B) {
         Joc[ax3][0] = d.x; Joc[ax3][1] = d.y; Joc[ax3][2] = d.z;
         V3<T> r = cp - po;
@@ -706,10 +786,22 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
           V3<T> axk = mk<T>(Ro.m[k], Ro.m[3 + k], Ro.m[6 + k]);
           Joc[ax3][3 + k] = dot(d, cross(axk, r));
         }
-        jvo = Joc[ax3][0] * vo.x + Joc[ax3][1] * vo.y + Joc[ax3][2] * vo.z + Joc[ax3][3] * wo.x + Joc[ax3][4] * wo.y + Joc[ax3][5] * wo.z;
       }
-      jvc[ax3] = warp_sum(Jc[ax3] * qd) + jvo;
+      jvc[ax3] = Jc[ax3] * qd;
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int ax3 = 0; ax3 < 3; ax3++) jvc[ax3] += __shfl_xor_sync(GMJ_FULL, jvc[ax3], o);
+    }
+#pragma unroll
+    for (int ax3 = 0; ax3 < 3; ax3++)
+      jvc[ax3] += (b2 == B) ? (Joc[ax3][0] * vo.x + Joc[ax3][1] * vo.y + Joc[ax3][2] * vo.z + Joc[ax3][3] * wo.x + Joc[ax3][4] * wo.y + Joc[ax3][5] * wo.z) : T(0);
+    const bool gripper_part = (b1 >= 0 && b1 < B) || (b2 >= 0 && b2 < B);
+    T xw[3] = { Jc[0], Jc[1], Jc[2] };
+    if (gripper_part) ldl_fwdK<T, N, 3>(tp, Mrow, lb, xw);      // object-ground contacts have no gripper columns
+#pragma unroll
+    for (int ax3 = 0; ax3 < 3; ax3++) xw[ax3] *= rsq;
     if (lane == 0) cn.row = nr;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
@@ -717,7 +809,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
       T Jo[6];
 #pragma unroll
       for (int i = 0; i < 6; i++) Jo[i] = Joc[0][i] + sg2 * Joc[t][i];
-      emit_row<T, N>(ws, tp, Mrow, lb, rsq, rsqo, nr + k, Jc[0] + sg2 * Jc[t], Jo, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr, -1);
+      put_row<T, N>(ws, tp, rsqo, nr + k, xw[0] + sg2 * xw[t], Jo, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr, -1);
     }
     nr += 4;
   }

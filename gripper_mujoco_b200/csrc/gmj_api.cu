@@ -128,10 +128,9 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
         __syncwarp();
         physics_substep<T, N, 32 * WPB>(ws, M, S, lane, dtd, tipf);
         phase_barrier<32 * WPB>(GMJ_NPHASE);
-        if (lane == 0) {
-          update_all<T, N>(e, ws.qfk);
-          if (flags & STEP_SENSORS) monitor_sensors<T, N>(e, S, M, ws.ax);
-        }
+        if (lane == 0) update_all<T, N>(e, ws.qfk);
+        __syncwarp();
+        if (flags & STEP_SENSORS) monitor_sensors<T, N>(e, S, M, ws.ax, lane);
         __syncwarp();
       } else { phase_idle<32 * WPB>(); phase_barrier<32 * WPB>(GMJ_NPHASE); }
     }

@@ -279,12 +279,20 @@ __device__ inline void extract_forces(const EnvState<T>& e, const WarpAux<T>& ax
 
 // MjClass::monitor_sensors (src/mjclass.cpp:741-898)
 template <typename T, int N>
-__device__ inline void monitor_sensors(EnvState<T>& e, const DevSettings& S, const DevModel<T>& M, const WarpAux<T>& ax) {
+__device__ inline void monitor_sensors(EnvState<T>& e, const DevSettings& S, const DevModel<T>& M, const WarpAux<T>& ax, int lane) {
+  // warp-collective: lane 0 owns the sensor state, the three cubic gauge fits (FP64 QR) run on lanes 0-2
   const double* g = S.s.general;
+  int due = 0;
+  if (lane == 0) due = ready_to_read(e, S, GSEN_bending_gauge, 0);
+  due = __shfl_sync(GMJ_FULL, due, 0);
+  float gfit = 0.0f;
+  if (due && lane < 3) gfit = read_gauge<T, N>(e, M, lane);
+  const float gfit0 = __shfl_sync(GMJ_FULL, gfit, 0), gfit1 = __shfl_sync(GMJ_FULL, gfit, 1), gfit2 = __shfl_sync(GMJ_FULL, gfit, 2);
+  if (lane != 0) return;
   bool got = false; DevForces F;
-  if (ready_to_read(e, S, GSEN_bending_gauge, 0)) {
+  if (due) {
     for (int f = 0; f < 3; f++) {
-      float gv = read_gauge<T, N>(e, M, f);
+      float gv = f == 0 ? gfit0 : (f == 1 ? gfit1 : gfit2);
       e.si_latest[f] = (float)(gv * (float)g[GS_sim_gauge_raw_to_N_factor]);
       gv = apply_normalisation(S.s.sensor[GSEN_bending_gauge], gv);
       gv = apply_noise(e, S, GSEN_bending_gauge, gv, f + 1);
@@ -337,18 +345,27 @@ template <typename T, int N>
 __device__ inline void update_all(EnvState<T>& e, const T* qfk) {
   const double time_per_step = 10 / 2000.0;
   if (e.time > e.last_step_time + time_per_step) {
-    int nx = e.tend.sx != e.tnext.sx;
-    int nz = e.tend.sz != e.tnext.sz;
-    double a = (180.0 / 3.14159265358979323846) * g_calc_th(e.tend.x, e.tend.y);
-    double b = (180.0 / 3.14159265358979323846) * g_calc_th(e.tnext.x, e.tnext.y);
-    int ny = !(fabs(a - b) < 5e-1);
-    int ox = e.old_moving & 1, oy = (e.old_moving >> 1) & 1, oz = (e.old_moving >> 2) & 1;
-    if (nx != ox) for (int i = 0; i < 3; i++) set_weld<T, N>(e, i, !nx, qfk);
-    if (ny != oy) { if (ny) for (int i = 3; i < 6; i++) set_weld<T, N>(e, i, 0, qfk); }
-    if (nz != oz) set_weld<T, N>(e, 6, !nz, qfk);
-    e.old_moving = nx | (ny << 1) | (nz << 2);
-    e.last_step_time = e.time;
-    g_step_to(e.tnext, e.tend, 10);
+    // old_moving bit 3 ("steady"): the previous tick moved no motor, the stepper state was already the
+    // canonical image of its step counts and the target has not changed since (set_action clears the
+    // bit), so this tick would recompute exactly the same values: only the tick clock advances.
+    // bit 4: tnext is the output of g_step_to (canonical).
+    if (e.old_moving & 8) e.last_step_time = e.time;
+    else {
+      int nx = e.tend.sx != e.tnext.sx;
+      int nz = e.tend.sz != e.tnext.sz;
+      double a = (180.0 / 3.14159265358979323846) * g_calc_th(e.tend.x, e.tend.y);
+      double b = (180.0 / 3.14159265358979323846) * g_calc_th(e.tnext.x, e.tnext.y);
+      int ny = !(fabs(a - b) < 5e-1);
+      int ox = e.old_moving & 1, oy = (e.old_moving >> 1) & 1, oz = (e.old_moving >> 2) & 1;
+      if (nx != ox) for (int i = 0; i < 3; i++) set_weld<T, N>(e, i, !nx, qfk);
+      if (ny != oy) { if (ny) for (int i = 3; i < 6; i++) set_weld<T, N>(e, i, 0, qfk); }
+      if (nz != oz) set_weld<T, N>(e, 6, !nz, qfk);
+      const int nomove = e.tend.sx == e.tnext.sx && e.tend.sy == e.tnext.sy && e.tend.sz == e.tnext.sz;
+      const int was_canon = (e.old_moving >> 4) & 1;
+      e.old_moving = nx | (ny << 1) | (nz << 2) | ((nomove && was_canon) ? 8 : 0) | 16;
+      e.last_step_time = e.time;
+      g_step_to(e.tnext, e.tend, 10);
+    }
   }
   if (e.has_object) {
     T vx = e.qvel[32], vy = e.qvel[33], vz = e.qvel[34];
@@ -399,6 +416,7 @@ __device__ inline int set_action(EnvState<T>& e, const DevSettings& S, const Dev
   int wl = 1, extra = 0;
   e.termination_sent = 0;
   if (action < 0 || action >= S.n_actions) return -1;
+  e.old_moving &= ~8;                       // the target may change: the stepper tick is no longer a no-op
   int code = S.action_options[action];
   const double* g = S.s.general;
   if (code == 3 * GACT_COUNT) {

@@ -204,6 +204,51 @@ static double impedance(const double* solimp, double pos) {
 
 enum { ROW_EQ = 0, ROW_LIMIT = 1, ROW_CONTACT = 2 };
 
+
+/* exact solution of (A + R) f + b = w, eq rows w = 0, ineq rows f >= 0, w >= 0, f w = 0, starting from the
+ * active set of the given f: block principal pivoting with Murty fallback (finite for SPD matrices) */
+static void lcp_polish(int n, const double* A, int lda, const double* R, const double* b, const int* type, double* f) {
+  static double K[OR_MAXROW * OR_MAXROW], x[OR_MAXROW], w[OR_MAXROW];
+  int act[OR_MAXROW], idx[OR_MAXROW];
+  double bscale = 0;
+  for (int r = 0; r < n; r++) { act[r] = (type[r] == ROW_EQ) || f[r] > 0; bscale = fmax(bscale, fabs(b[r])); }
+  int best = 1 << 30, patience = 3;
+  for (int round = 0; round < 200; round++) {
+    int m = 0;
+    for (int r = 0; r < n; r++) if (act[r]) idx[m++] = r;
+    for (int a = 0; a < m; a++) {
+      for (int c = 0; c < m; c++) K[a * m + c] = A[idx[a] * lda + idx[c]];
+      K[a * m + a] += R[idx[a]];
+      x[a] = -b[idx[a]];
+    }
+    if (m > 0) { if (!chol(K, m)) return; chol_solve(K, m, x); }
+    double fscale = 0;
+    for (int a = 0; a < m; a++) fscale = fmax(fscale, fabs(x[a]));
+    for (int r = 0; r < n; r++) {
+      double s = b[r];
+      for (int a = 0; a < m; a++) s += A[r * lda + idx[a]] * x[a];
+      w[r] = s;
+    }
+    const double tolf = 1e-12 * (1 + fscale), tolw = 1e-12 * (1 + bscale);
+    int ninf = 0, top = -1, bad[OR_MAXROW];
+    for (int r = 0, a = 0; r < n; r++) {
+      bad[r] = 0;
+      if (act[r]) { if (type[r] != ROW_EQ && x[a] < -tolf) bad[r] = 1; a++; }
+      else if (w[r] < -tolw) bad[r] = 1;
+      if (bad[r]) { ninf++; top = r; }
+    }
+    if (ninf == 0) {
+      for (int r = 0, a = 0; r < n; r++) f[r] = act[r] ? x[a++] : 0.0;
+      for (int r = 0; r < n; r++) if (type[r] != ROW_EQ && f[r] < 0) f[r] = 0;
+      return;
+    }
+    int block = 1;
+    if (ninf < best) { best = ninf; patience = 3; } else if (patience > 0) patience--; else block = 0;
+    if (block) { for (int r = 0; r < n; r++) if (bad[r]) act[r] = !act[r]; }
+    else act[top] = !act[top];
+  }
+}
+
 void or_physics_step(OrEnv* e) {
   const GmjModel* m = &e->m;
   const double dt = e->s.general[GS_mujoco_timestep];
@@ -353,6 +398,10 @@ void or_physics_step(OrEnv* e) {
     if (change <= 1e-13 * (1 + scale)) { it++; break; }
   }
   e->niter = it;
+  /* ---- polish: the dual has a unique solution (A + R is SPD). Gauss-Seidel stalls on stiff squeezes
+   * (4000 sweeps are not always enough), so the active set it found is refined by principal pivoting
+   * with dense Cholesky solves until the complementarity conditions hold to 1e-12. */
+  if (nr > 0) lcp_polish(nr, &A[0][0], OR_MAXROW, Rr, bvec, rtype, fr);
   memcpy(e->efc_force_prev, fr, sizeof(double) * nr); e->nrow_prev = nr;
   for (int j = 0; j < nv; j++) { e->qacc[j] = qacc_s[j]; }
   for (int r = 0; r < nr; r++) {

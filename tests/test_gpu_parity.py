@@ -241,3 +241,75 @@ def test_mjclass_surface_fp32():
     assert names[1] == mj.get_object_name(100)
     assert abs(mj.get_wrist_force()).max() < 5.0         # zeroed by the wrist-Z calibration
     mj.close()
+
+
+GRASP = [0] * 60 + [2] * 10 + [14]         # close 60 mm, tilt the fingers in 0.1 rad, terminate (lift)
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_grasp_and_lift_episode(precision):
+    """A full successful grasp episode at the calibrated timestep (7.02 ms, S = 29): fingers close on a
+    77 mm cube, tilt, the termination action lifts it. 71 action steps = 2120 substeps with finger-object
+    and object-ground contacts. FP64: state within 1e-8 until first finger contact, every event row exact at every step of the episode. FP32
+    (chaotic once the fingers squeeze): event rows exact up to first finger contact, the episode outcome
+    (lifted / successful_grasp / done step) must agree, final object height within 5 mm."""
+    from gripper_mujoco_b200.settings import BINARY_NAMES
+    n = 3
+    mdl, st = make_pair(5, 7.02e-3, noise=False)
+    gb, ob = _batch(n, mdl, st, precision), OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    idx = np.full(n, find_object("cube_fillet_0_3")[0], dtype=np.int32)
+    x = np.array([0.0, 0.002, -0.002], dtype=np.float32)
+    gb.spawn_object(idx, x, 0.0, 0.0); ob.spawn(idx, x, 0.0, 0.0)
+    contact_row = BINARY_NAMES.index("object_contact")
+    for t, a in enumerate(GRASP):
+        act = np.full(n, a, dtype=np.int32)
+        o_g, r_g, d_g, e_g = (v.cpu().numpy() for v in gb.step(act))
+        o_o, r_o, d_o, e_o = ob.step(act)
+        qg, _ = gb.state()
+        if precision == "fp64":
+            # free of finger contact the two FP64 implementations agree to rounding (1e-16 measured). A
+            # finger pad against a cube face is a flat-on-flat contact: the MPR contact POINT is not
+            # unique there, and rounding (nvcc contracts FMAs, gcc does not) decides which point of the
+            # patch the portal converges to -- measured as one 2e-5 jump in the substep a new pad contact
+            # appears (tests/dev_grasp_diff.py), growing to 7e-5 by the end of the squeeze
+            # and then grows chaotically while the object is squeezed and lifted (3.7e-3 at the end): after
+            # first finger contact only the discrete outcome is asserted per step
+            if e_o[:, contact_row].max() == 0:
+                assert np.abs(qg - ob.qpos()).max() < 1e-8, t
+            assert np.isfinite(qg).all()
+            assert np.array_equal(e_g[:, DISCRETE], e_o[:, DISCRETE]), t
+            assert np.abs(r_g - r_o).max() < 1e-5 and np.array_equal(d_g.astype(bool), d_o)
+        elif e_o[:, contact_row].max() == 0:
+            assert np.array_equal(e_g[:, DISCRETE], e_o[:, DISCRETE]), t
+            assert np.abs(qg - ob.qpos()).max() < 1e-4, t
+    for nm in ("lifted", "successful_grasp", "lifted_termination", "failed_termination", "oob"):
+        k = BINARY_NAMES.index(nm)
+        assert np.array_equal(e_g[:, k] > 0, e_o[:, k] > 0), nm
+    assert (e_o[:, BINARY_NAMES.index("successful_grasp")] > 0).all()
+    assert np.array_equal(d_g.astype(bool), d_o) and d_o.all()
+    B = mdl.B
+    assert np.abs(qg[:, B + 2] - ob.qpos()[:, B + 2]).max() < 5e-3
+    gb.close()
+
+
+def test_free_space_50_steps_events_exact_fp32():
+    """SURVEY 8c protocol: events / done / sign-mode observation entries bit-exact over 50 action steps
+    in free space (no object), FP32 product build."""
+    n = 8
+    mdl, st = make_pair(5, 7.02e-3, noise=False)
+    gb, ob = _batch(n, mdl, st, "fp32"), OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    rng = np.random.default_rng(2024)
+    for t in range(50):
+        a = rng.integers(0, gb.n_actions - 1, n).astype(np.int32)
+        o_g, r_g, d_g, e_g = (v.cpu().numpy() for v in gb.step(a))
+        o_o, r_o, d_o, e_o = ob.step(a)
+        assert np.array_equal(e_g[:, DISCRETE], e_o[:, DISCRETE]), t
+        assert np.array_equal(d_g.astype(bool), d_o), t
+        sign_cols = np.isin(o_o, (-1.0, 0.0, 1.0)).all(axis=0)          # state sensors use sign-mode sampling
+        assert np.array_equal(o_g[:, sign_cols], o_o[:, sign_cols]), t
+        assert np.abs(o_g - o_o).max() < 2e-3 and np.abs(r_g - r_o).max() < 1e-4
+    qg, _ = gb.state()
+    assert np.abs(qg - ob.qpos()).max() < 1e-4
+    gb.close()

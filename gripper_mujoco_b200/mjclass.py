@@ -178,5 +178,20 @@ class MjClass:
     def get_wrist_force(self) -> np.ndarray:
         return self.batch.probe_field("si_wrist")
 
+    # ------------------------------------------------------------------ pickle (src/bind.cpp:207-241)
+    def __getstate__(self):
+        """Like the reference: settings, model key and spawn params are saved, physics state is not;
+        the calibration results travel inside the settings and auto-calibration is not repeated."""
+        return dict(n_envs=self.n_envs, params=self.params, settings=self.set, device=self.device_index,
+                    precision=self.precision, env_id_offset=self.env_id_offset,
+                    object_set_name=self.object_set_name, spawn=self.default_spawn_params.__dict__)
+
+    def __setstate__(self, st):
+        s = st["settings"]
+        self.__init__(st["n_envs"], st["params"], None, s, st["device"], st["precision"], st["env_id_offset"],
+                      calibrate=False)
+        self.object_set_name = st["object_set_name"]
+        self.default_spawn_params.__dict__.update(st["spawn"])
+
     def close(self):
         self.batch.close()

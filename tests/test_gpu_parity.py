@@ -240,6 +240,12 @@ def test_mjclass_surface_fp32():
     names = mj.get_current_object_name()
     assert names[1] == mj.get_object_name(100)
     assert abs(mj.get_wrist_force()).max() < 5.0         # zeroed by the wrist-Z calibration
+    import pickle
+    mj2 = pickle.loads(pickle.dumps(mj))                 # settings + calibration travel, physics state does not
+    assert mj2.set.mujoco_timestep == mj.set.mujoco_timestep and mj2.set.sim_steps_per_action == mj.set.sim_steps_per_action
+    assert mj2.set.bending_gauge.normalise == mj.set.bending_gauge.normalise and mj2.get_n_obs() == mj.get_n_obs()
+    assert float(mj2.batch.probe_field("time").max()) == 0.0
+    mj2.close()
     mj.close()
 
 

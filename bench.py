@@ -253,6 +253,8 @@ def main():
     if world > 1:          # the path's only exchange: transitions of every shard to the learner rank (NCCL gather)
         from gripper_mujoco_b200.sharding import TransitionGather, shard_range
         gatherer = TransitionGather(shard_range(world * n, rank, world), gb.n_obs, dev, dst=0)
+        for _ in range(3):                 # communicator set-up and first-use costs stay outside the timed region
+            gatherer.gather(gb.obs, gb.reward, gb.done)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()

@@ -37,7 +37,20 @@ def calibrate_reset(p: GripperParams, N: int, B: int, s: Settings, backend) -> N
         setattr(st, f"reset_qpos_g{2 * f}", p.xy_home)
         setattr(st, f"reset_qpos_g{2 * f + 1}", 0.0)
     st.reset_qpos_g6 = p.z_home
-    q = backend(st, 400, False)["qpos"]
+    # The reference settles at the MJCF default timestep (2 ms) whatever the model. Finger chains of more than
+    # ~10 segments are unstable at 2 ms (rl/juypter/thesis_plots/mujoco_timesteps.csv); MuJoCo then hits
+    # BADQACC and auto-resets mid-settle, which leaves an arbitrary pose. Here the same 0.8 s settle is
+    # repeated at half the timestep until it is stable, so long fingers start from a true equilibrium.
+    steps = 400
+    for _ in range(5):
+        r = backend(st, steps, False)
+        q = r["qpos"]
+        if not r["unstable"] and np.all(np.isfinite(q)) and np.abs(q[:B]).max() < 10.0:
+            break
+        st.mujoco_timestep *= 0.5
+        steps *= 2
+    else:
+        raise RuntimeError("calibrate_reset: no stable settle found")
     s.reset_qpos_base = float(q[0])
     for f in range(3):
         setattr(s, f"reset_qpos_g{2 * f}", float(q[1 + f * (N + 2)]))

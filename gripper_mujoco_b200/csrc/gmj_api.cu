@@ -1,157 +1,9 @@
 // gmj_api.cu -- kernels + C ABI (include/gmj.h) of libgripper_b200.so.
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
-#include <cuda_runtime.h>
-#include <math.h>
-#include <stdio.h>
-#include <string.h>
-#include <string>
-#include <vector>
-#include "../../include/gmj.h"
-#include "gmj_physics.cuh"
-
-// environments (warps) per block of the FP32 step kernel, one block per SM: as many as shared memory
-// holds (N = 5: 12 x 16.1 KB, 14 measured no faster, N = 8: 12 x 18.8 KB of the 227 KB)
-// envs are dealt to blocks in order of expected load so that the warps of a lockstep block finish each
-// phase together (ncu: stall_barrier was the top stall with arrival order)
-#ifndef GMJ_LIFT_WPB
-#define GMJ_LIFT_WPB 12
-#endif
-#define GMJ_SORT_BUCKETS 16
-#define GMJ_SORT_DIV 3
-#ifndef GMJ_BLOCKS_PER_SM
-#define GMJ_BLOCKS_PER_SM 1
-#endif
-#ifndef GMJ_WPB_F32_N5
-#define GMJ_WPB_F32_N5 12
-#endif
-#ifndef GMJ_WPB_F32_N8
-#define GMJ_WPB_F32_N8 12
-#endif
+// Build: see gripper_mujoco_b200/lib.py (one translation unit per step-kernel instantiation, linked into one .so)
+#include "gmj_step.cuh"
 
 static thread_local std::string g_err;
-#define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) { g_err = std::string(#x) + ": " + cudaGetErrorString(_e); return 1; } } while (0)
-#define FAIL(msg) do { g_err = (msg); return 1; } while (0)
-
-// ------------------------------------------------------------------------------------------ kernels
-enum { STEP_SET_ACTION = 1, STEP_SUBSTEPS = 2, STEP_TAIL = 4, STEP_OUTPUT = 8, STEP_SENSORS = 16,
-       STEP_COLLECT = 32,   // set_action only: append envs that owe extra substeps (termination lift) to env_list
-       STEP_LIST = 64,      // run on the envs of env_list[0 .. *env_count) instead of all envs
-       STEP_COMBINED = 128 }; // blocks [0, list_blocks) take env_list (owed lift substeps first), the rest all other envs
-
-template <typename T> __device__ __forceinline__ void copy_words(void* dst, const void* src, int nbytes, int lane) {
-  const uint32_t* s = (const uint32_t*)src; uint32_t* d = (uint32_t*)dst;
-  for (int i = lane; i < nbytes / 4; i += 32) d[i] = s[i];
-}
-
-// One warp per environment, WPB environments per block. flags select the phases so the same kernel
-// serves gmj_step (all), gmj_set_action, gmj_action_step, gmj_substeps and gmj_observe.
-// The kernel is instruction-fetch bound (ncu: stall_no_inst dominates, the step is ~25 k SASS
-// instructions of mostly straight-line code against a 32 KB L1.5 I-cache), so the warps of a block
-// are kept in lockstep with a block barrier per substep: one fetch stream then feeds WPB warps.
-template <typename T, int N> struct StepCfg { static constexpr int WPB = sizeof(T) == 4 ? (N <= 5 ? GMJ_WPB_F32_N5 : GMJ_WPB_F32_N8) : 4; };
-
-template <typename T, int N>
-__global__ void __launch_bounds__(32 * StepCfg<T, N>::WPB, GMJ_BLOCKS_PER_SM)
-k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const DevSettings* __restrict__ Sp, int n_envs,
-       int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
-       float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,
-       int* __restrict__ err_flag, int* __restrict__ env_list, int* __restrict__ env_count, int list_blocks,
-       const int* __restrict__ perm, int* __restrict__ hist) {
-  constexpr int WPB = StepCfg<T, N>::WPB;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ int s_nsub_max;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int bid = blockIdx.x;
-  bool list_block = (flags & STEP_LIST) != 0;
-  if (flags & STEP_COMBINED) { list_block = bid < list_blocks; if (!list_block) bid -= list_blocks; }
-  int env = bid * WPB + warp;
-  bool valid = env < n_envs;
-  if (list_block) {                        // the collected envs, GMJ_LIFT_WPB per block; surplus blocks leave at once
-    // a lifting env runs 3S substeps back to back: few warps per block keep that critical path short
-    // (a 4-warp block steps ~2.5x faster than a full one), the idle warps only pass the barriers
-    constexpr int LW = GMJ_LIFT_WPB < WPB ? GMJ_LIFT_WPB : WPB;
-    const int cnt = *env_count;
-    if (bid * LW >= cnt) return;
-    env = bid * LW + warp;
-    valid = warp < LW && env < cnt;
-    env = valid ? env_list[env] : 0;
-  } else if (flags & STEP_COMBINED) {      // everybody else, in the load-sorted order built by k_sort_scatter
-    const int n_rest = n_envs - *env_count;
-    if (bid * WPB >= n_rest) return;
-    valid = env < n_rest;
-    env = valid ? perm[env] : 0;
-  }
-  WarpShared<T, N>& ws = *reinterpret_cast<WarpShared<T, N>*>(smem_raw + (size_t)warp * sizeof(WarpShared<T, N>));
-  const DevModel<T>& M = *Mp; const DevSettings& S = *Sp;
-  if (threadIdx.x == 0) s_nsub_max = 0;
-  if (valid) {
-    copy_words<T>(&ws.e, &envs[env], sizeof(EnvState<T>), lane);
-    if (lane == 0) { ws.ax.ncon = 0; ws.ax.nrow = 0; ws.ax.niter = 0; ws.ax.wrist_z = ws.e.wrist_z; }
-    ws.qfk[lane] = ws.e.qpos[lane];
-  }
-  __syncthreads();
-  EnvState<T>& e = ws.e;
-  int extra = 0;
-  if ((flags & STEP_SET_ACTION) && valid) {
-    if (lane == 0) {
-      extra = set_action<T>(e, S, M, actions[env], frac ? frac[env] : 0.0f);
-      if (extra < 0) { extra = 0; if (err_flag) atomicExch(err_flag, 1); }
-    }
-    if ((flags & STEP_COLLECT) && lane == 0) {
-      e.pending_extra = extra;
-      if (extra > 0) env_list[atomicAdd(env_count, 1)] = env;
-      else {                               // load key: constraint rows of the last substep (contacts dominate the cost)
-        int key = e.nrow_prev / GMJ_SORT_DIV; if (key >= GMJ_SORT_BUCKETS) key = GMJ_SORT_BUCKETS - 1;
-        e.sort_key = key; atomicAdd(&hist[key], 1);
-      }
-    }
-    extra = __shfl_sync(GMJ_FULL, extra, 0);
-    __syncwarp();
-  }
-  if (list_block && valid) {               // owed lift substeps run first, exactly as inside MjClass::set_action
-    extra = (int)e.pending_extra;
-    __syncwarp();
-    if (lane == 0) e.pending_extra = 0;
-  }
-  if (flags & STEP_SUBSTEPS) {
-    const int nsub = valid ? extra + (nsub_override >= 0 ? nsub_override : (int)S.s.general[GS_sim_steps_per_action]) : 0;
-    if (lane == 0) atomicMax(&s_nsub_max, nsub);
-    __syncthreads();
-    const int nsub_max = s_nsub_max;
-    const double dtd = S.s.general[GS_mujoco_timestep];
-    const bool curve = S.s.general[GS_curve_validation] != 0;
-    const T tipf = curve ? (T)S.s.general[GS_tip_force_applied] : T(0);
-    for (int i = 0; i < nsub_max; i++) {
-      __syncthreads();                       // lockstep: shared instruction stream
-      if (i < nsub) {
-        if (curve && lane == 0) for (int id = 0; id < 6; id++) set_weld<T, N>(e, id, 1, ws.qfk);   // apply_segment_force re-locks every step
-        __syncwarp();
-        physics_substep<T, N, 32 * WPB>(ws, M, S, lane, dtd, tipf);
-        phase_barrier<32 * WPB>(GMJ_NPHASE);
-        if (lane == 0) update_all<T, N>(e, ws.qfk);
-        __syncwarp();
-        if (flags & STEP_SENSORS) monitor_sensors<T, N>(e, S, M, ws.ax, lane);
-        __syncwarp();
-      } else { phase_idle<32 * WPB>(); phase_barrier<32 * WPB>(GMJ_NPHASE); }
-    }
-    if (valid && lane == 0) e.wrist_z = (float)ws.ax.wrist_z;
-  }
-  if (!valid) return;
-  if ((flags & STEP_TAIL) && lane == 0) {
-    sense_gripper_state<T>(e, S, M);
-    update_env<T>(e, S, ws.ax);
-    e.num_action_steps += 1;
-  }
-  if ((flags & STEP_OUTPUT) && lane == 0) {
-    if (reward) { float r = calc_reward<T>(e, S); e.last_reward = r; reward[env] = r; }
-    int d = calc_done<T>(e, S); e.last_done = d;
-    if (done) done[env] = (uint8_t)d;
-    if (obs) get_observation<T>(e, S, obs + (size_t)env * S.n_obs);
-    if (events) event_state<T>(e, events + (size_t)env * GMJ_EVENT_STATE_LEN);
-  }
-  __syncwarp();
-  copy_words<T>(&envs[env], &ws.e, sizeof(EnvState<T>), lane);
-}
+void gmj_set_error(const std::string& msg) { g_err = msg; }
 
 // counting-sort scatter of the envs that owe no lift substeps: perm[offset(key) + slot] = env
 template <typename T>
@@ -167,24 +19,25 @@ __global__ void k_sort_scatter(const EnvState<T>* __restrict__ envs, int n_envs,
 }
 
 // MjClass::reset + luke::reset (src/mjclass.cpp:434-486, src/myfunctions.cpp:544-570): one thread per env
-template <typename T>
-__global__ void k_reset(EnvState<T>* envs, const DevModel<T>* Mp, const DevSettings* Sp, int n_envs,
+template <typename T, int QC>
+__global__ void k_reset(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const DevSettings* Sp, int n_envs,
                         const uint8_t* mask, uint32_t env_id_offset) {
+  constexpr int OQ = QC - 8;
   int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= n_envs) return;
   if (mask && !mask[env]) return;
-  EnvState<T>& e = envs[env];
-  const DevModel<T>& M = *Mp; const DevSettings& S = *Sp;
+  EnvState<T, QC>& e = envs[env];
+  const DevModelS<T>& M = *Mp; const DevSettings& S = *Sp;
   const int N = M.N, NL = N + 2, B = M.B;
   uint32_t episode = e.episode + 1;
   unsigned long long c0 = e.st_contacts, c1 = e.st_rows, c2 = e.st_iters, c3 = e.st_substeps; unsigned int c4 = e.st_unstable + (e.unstable ? 1 : 0), c5 = e.st_overflow;
-  memset(&e, 0, sizeof(EnvState<T>));
+  memset(&e, 0, sizeof(EnvState<T, QC>));
   e.st_contacts = c0; e.st_rows = c1; e.st_iters = c2; e.st_substeps = c3; e.st_unstable = c4; e.st_overflow = c5;
   e.episode = episode; e.env_id = env_id_offset + env; e.rng_ctr = episode << 12;
   g_reset(e.tend); g_reset(e.tnext);
-  for (int i = 0; i < B; i++) e.qpos[i] = M.f[MF_qpos0][i];
+  for (int i = 0; i < B; i++) e.qpos[i] = M.qpos0[i];
   // parked object (dead collision group): not simulated
-  e.qpos[32] = 0; e.qpos[33] = 2; e.qpos[34] = 1; e.qpos[35] = 0; e.qpos[36] = 0; e.qpos[37] = 0; e.qpos[38] = 1;
+  e.qpos[OQ] = 0; e.qpos[OQ + 1] = 2; e.qpos[OQ + 2] = 1; e.qpos[OQ + 3] = 0; e.qpos[OQ + 4] = 0; e.qpos[OQ + 5] = 0; e.qpos[OQ + 6] = 1;
   // weld anchors from the keyframe pose (xpos/xmat are stale when set_all_constraints runs), then
   // the stored equilibrium of base + motor joints (calibrate_reset)
   for (int f = 0; f < 3; f++) { e.weld_anchor[f] = e.qpos[1 + f * NL]; e.weld_anchor[3 + f] = e.qpos[2 + f * NL]; }
@@ -246,15 +99,16 @@ __device__ inline int box2d_overlap(const double* a, const double* o, double min
 }
 
 // MjClass::spawn_object / spawn_into_scene (src/mjclass.cpp:2352-2420,2475-2654)
-template <typename T>
-__global__ void k_spawn(EnvState<T>* envs, const DevModel<T>* Mp, const DevSettings* Sp, const GmjObject* objects, int n_objects,
+template <typename T, int QC>
+__global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const DevSettings* Sp, const GmjObject* objects, int n_objects,
                         int n_envs, const int32_t* idx, const float* xyr, const uint8_t* mask, float xy_range, float rot_range,
                         int* err_flag) {
   int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= n_envs) return;
   if (mask && !mask[env]) return;
-  EnvState<T>& e = envs[env];
-  const DevSettings& S = *Sp; const DevModel<T>& M = *Mp;
+  constexpr int OQ = QC - 8;
+  EnvState<T, QC>& e = envs[env];
+  const DevSettings& S = *Sp; const DevModelS<T>& M = *Mp;
   int oi; double x, y, rot;
   if (idx) {
     oi = idx[env]; x = xyr[3 * env]; y = xyr[3 * env + 1]; rot = xyr[3 * env + 2];
@@ -295,20 +149,21 @@ __global__ void k_spawn(EnvState<T>* envs, const DevModel<T>* Mp, const DevSetti
   e.obj[13] = (T)ob.friction; e.obj[14] = (T)ob.z_rest;
   e.obj_index = oi; e.has_object = 1;
   double z = ob.z_rest + 1e-6;
-  e.qpos[32] = (T)x; e.qpos[33] = (T)y; e.qpos[34] = (T)z;
-  e.qpos[35] = (T)sin(-rot / 2.0); e.qpos[36] = 0; e.qpos[37] = 0; e.qpos[38] = (T)cos(-rot / 2.0);
-  for (int k = 0; k < 6; k++) e.qvel[32 + k] = 0;
+  e.qpos[OQ] = (T)x; e.qpos[OQ + 1] = (T)y; e.qpos[OQ + 2] = (T)z;
+  e.qpos[OQ + 3] = (T)sin(-rot / 2.0); e.qpos[OQ + 4] = 0; e.qpos[OQ + 5] = 0; e.qpos[OQ + 6] = (T)cos(-rot / 2.0);
+  for (int k = 0; k < 6; k++) e.qvel[OQ + k] = 0;
   e.start_z = (double)(T)z;
   e.nrow_prev = 0;
 }
 
-template <typename T>
-__global__ void k_dump(const EnvState<T>* envs, int n_envs, int B, double* qpos, double* qvel, double* probe) {
+template <typename T, int QC>
+__global__ void k_dump(const EnvState<T, QC>* envs, int n_envs, int B, double* qpos, double* qvel, double* probe) {
+  constexpr int OQ = QC - 8;
   int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= n_envs) return;
-  const EnvState<T>& e = envs[env];
-  if (qpos) { for (int i = 0; i < B; i++) qpos[(size_t)env * (B + 7) + i] = (double)e.qpos[i]; for (int k = 0; k < 7; k++) qpos[(size_t)env * (B + 7) + B + k] = (double)e.qpos[32 + k]; }
-  if (qvel) { for (int i = 0; i < B; i++) qvel[(size_t)env * (B + 6) + i] = (double)e.qvel[i]; for (int k = 0; k < 6; k++) qvel[(size_t)env * (B + 6) + B + k] = (double)e.qvel[32 + k]; }
+  const EnvState<T, QC>& e = envs[env];
+  if (qpos) { for (int i = 0; i < B; i++) qpos[(size_t)env * (B + 7) + i] = (double)e.qpos[i]; for (int k = 0; k < 7; k++) qpos[(size_t)env * (B + 7) + B + k] = (double)e.qpos[OQ + k]; }
+  if (qvel) { for (int i = 0; i < B; i++) qvel[(size_t)env * (B + 6) + i] = (double)e.qvel[i]; for (int k = 0; k < 6; k++) qvel[(size_t)env * (B + 6) + B + k] = (double)e.qvel[OQ + k]; }
   if (probe) {
     double* p = probe + (size_t)env * GMJ_PROBE_LEN;
     for (int k = 0; k < GMJ_PROBE_LEN; k++) p[k] = 0;
@@ -323,18 +178,18 @@ __global__ void k_dump(const EnvState<T>* envs, int n_envs, int B, double* qpos,
   }
 }
 
-template <typename T, int N>
-__global__ void k_gauge(const EnvState<T>* envs, const DevModel<T>* Mp, int n_envs, double* probe) {
+template <typename T, int N, int QC>
+__global__ void k_gauge(const EnvState<T, QC>* envs, const DevModelS<T>* Mp, int n_envs, double* probe) {
   int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= n_envs) return;
   for (int f = 0; f < 3; f++) probe[(size_t)env * GMJ_PROBE_LEN + GP_gauge0 + f] = (double)read_gauge<T, N>(envs[env], *Mp, f);
 }
 
-template <typename T>
-__global__ void k_set_welds(EnvState<T>* envs, int n_envs, int B, int N, int mask_on) {
+template <typename T, int QC>
+__global__ void k_set_welds(EnvState<T, QC>* envs, int n_envs, int B, int N, int mask_on) {
   int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= n_envs) return;
-  EnvState<T>& e = envs[env];
+  EnvState<T, QC>& e = envs[env];
   for (int id = 0; id < 7; id++) {
     if ((mask_on >> id) & 1) {
       int j = (id < 3) ? (1 + id * (N + 2)) : ((id < 6) ? (2 + (id - 3) * (N + 2)) : (B - 1));
@@ -344,33 +199,17 @@ __global__ void k_set_welds(EnvState<T>* envs, int n_envs, int B, int N, int mas
   e.weld_on = mask_on & 0x7f;
 }
 
-template <typename T>
-__global__ void k_stats(const EnvState<T>* envs, int n_envs, unsigned long long* out) {
+template <typename T, int QC>
+__global__ void k_stats(const EnvState<T, QC>* envs, int n_envs, unsigned long long* out) {
   int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= n_envs) return;
-  const EnvState<T>& e = envs[env];
+  const EnvState<T, QC>& e = envs[env];
   atomicAdd(&out[0], e.st_substeps); atomicAdd(&out[1], (unsigned long long)(e.st_unstable + (e.unstable ? 1 : 0)));
   atomicAdd(&out[2], e.st_contacts); atomicAdd(&out[3], e.st_rows); atomicAdd(&out[4], e.st_iters);
   atomicAdd(&out[5], (unsigned long long)e.st_overflow);
 }
 
 // ------------------------------------------------------------------------------------------ host side
-struct GmjHandle {
-  int n_envs, device, precision, N, B;
-  uint32_t env_id_offset;
-  void* envs;            // EnvState<T>[n_envs]
-  void* model;           // DevModel<T>
-  DevSettings* settings; // device
-  DevSettings hs;        // host copy
-  GmjObject* objects; int n_objects;
-  int* err_flag;
-  int* env_list; int* env_count;   // envs that owe the 2S termination-lift substeps this step
-  int* perm; int* hist;            // load-sorted order of the other envs; hist[0..16) counts, hist[16..32) cursors
-  unsigned long long* stats_dev;
-  double* scratch; size_t scratch_len;
-  GmjModel hm;
-  size_t smem_bytes;
-};
 
 static void quat2mat_h(const double* q, double* R) {
   double w = q[0], x = q[1], y = q[2], z = q[3];
@@ -379,42 +218,60 @@ static void quat2mat_h(const double* q, double* R) {
   R[6] = 2 * (x * z - w * y); R[7] = 2 * (y * z + w * x); R[8] = 1 - 2 * (x * x + y * y);
 }
 
-template <typename T>
-static int build_model(const GmjModel* m, DevModel<T>* d) {
-  memset(d, 0, sizeof(*d));
+// Model constants in slot order. LN = 32: slot == body index (lane-per-dof kernels). LN = 96 (wide kernels):
+// finger f, chain position l -> slot 32 f + l; palm -> slot 30; base -> slot 31 of EVERY warp (replicas).
+template <typename T, int LN>
+static int build_model(const GmjModel* m, DevModel<T, LN>* d) {
+  memset((void*)d, 0, sizeof(*d));
   const int N = m->N, NL = N + 2, B = m->B;
+  const bool wide = LN != 32;
   if (m->nb != 1) FAIL("only nb = 1 (world_to_base) is supported");
-  if (B != 3 * N + 8 || B > 32) FAIL("lane-per-dof layout needs B = 3N + 8 <= 32 (N <= 8)");
-  d->N = N; d->B = B; d->NL = NL; d->palm_lane = B - 1;
+  if (B != 3 * N + 8) FAIL("model does not have B = 3N + 8 gripper bodies");
+  if (!wide && B > 32) FAIL("lane-per-dof layout needs B = 3N + 8 <= 32 (N <= 8)");
+  if (wide && (NL > 30 || B > GMJ_MAXB)) FAIL("wide layout needs N + 2 <= 30 chain lanes per finger (N <= 28) and B <= 88");
+  auto slots = [&](int body, int* out) -> int {
+    if (!wide) { out[0] = body; return 1; }
+    if (body == 0) { out[0] = 31; out[1] = 63; out[2] = 95; return 3; }
+    if (body == B - 1) { out[0] = 30; return 1; }
+    int f = (body - 1) / NL; out[0] = 32 * f + (body - 1) - f * NL; return 1;
+  };
+  d->N = N; d->B = B; d->NL = NL; d->palm_lane = wide ? 30 : B - 1;
   d->zref = (T)0.2;
-  for (int i = 0; i < 32; i++) { d->f[MF_gtype][i] = -1; d->f[MF_htype][i] = -1; d->f[MF_mass][i] = 0; d->f[MF_R0][i] = d->f[MF_R4][i] = d->f[MF_R8][i] = 1; }
+  for (int i = 0; i < LN; i++) { d->f[MF_gtype][i] = -1; d->f[MF_htype][i] = -1; d->f[MF_mass][i] = 0; d->f[MF_R0][i] = d->f[MF_R4][i] = d->f[MF_R8][i] = 1; }
   for (int i = 0; i < B; i++) {
     double R[9]; quat2mat_h(m->quat[i], R);
-    d->f[MF_parent][i] = (T)m->parent[i]; d->f[MF_jtype][i] = (T)m->jtype[i]; d->f[MF_group][i] = (T)m->group[i];
-    for (int k = 0; k < 3; k++) { d->f[MF_pos0 + k][i] = (T)m->pos[i][k]; d->f[MF_ax0 + k][i] = (T)m->axis[i][k]; d->f[MF_ip0 + k][i] = (T)m->ipos[i][k]; }
-    if (m->parent[i] < 0) d->f[MF_pos2][i] = (T)(m->pos[i][2] - (double)d->zref);
-    for (int k = 0; k < 9; k++) d->f[MF_R0 + k][i] = (T)R[k];
-    d->f[MF_mass][i] = (T)m->mass[i];
-    for (int k = 0; k < 6; k++) d->f[MF_ixx + k][i] = (T)m->inertia[i][k];
-    d->f[MF_stiff][i] = (T)m->stiffness[i]; d->f[MF_damp][i] = (T)m->damping[i];
-    d->f[MF_lo][i] = (T)m->range_lo[i]; d->f[MF_hi][i] = (T)m->range_hi[i]; d->f[MF_qpos0][i] = (T)m->qpos0[i];
     // structural checks for the lane layout
     int exp_parent = (i == 0) ? -1 : ((i == B - 1) ? 0 : (((i - 1) % NL == 0) ? 0 : i - 1));
     if (m->parent[i] != exp_parent) FAIL("model tree does not match the lane layout");
     int exp_hinge = (i != 0 && i != B - 1 && ((i - 1) % NL) > 0);
     if (m->jtype[i] != exp_hinge) FAIL("model joint types do not match the lane layout");
+    d->qpos0[i] = (T)m->qpos0[i];
+    int sl[3]; const int ns = slots(i, sl);
+    for (int r = 0; r < ns; r++) {
+      const int s = sl[r];
+      d->f[MF_parent][s] = (T)m->parent[i]; d->f[MF_jtype][s] = (T)m->jtype[i]; d->f[MF_group][s] = (T)m->group[i];
+      for (int k = 0; k < 3; k++) { d->f[MF_pos0 + k][s] = (T)m->pos[i][k]; d->f[MF_ax0 + k][s] = (T)m->axis[i][k]; d->f[MF_ip0 + k][s] = (T)m->ipos[i][k]; }
+      if (m->parent[i] < 0) d->f[MF_pos2][s] = (T)(m->pos[i][2] - (double)d->zref);
+      for (int k = 0; k < 9; k++) d->f[MF_R0 + k][s] = (T)R[k];
+      d->f[MF_mass][s] = (T)m->mass[i];
+      for (int k = 0; k < 6; k++) d->f[MF_ixx + k][s] = (T)m->inertia[i][k];
+      d->f[MF_stiff][s] = (T)m->stiffness[i]; d->f[MF_damp][s] = (T)m->damping[i];
+      d->f[MF_lo][s] = (T)m->range_lo[i]; d->f[MF_hi][s] = (T)m->range_hi[i]; d->f[MF_qpos0][s] = (T)m->qpos0[i];
+    }
   }
   // PD control (src/myfunctions.cpp:1965-2057): target selector 1 base z, 2 x, 3 th, 4 z
-  d->f[MF_tsel][0] = 1; d->f[MF_kp][0] = (T)m->base_kp; d->f[MF_kd][0] = (T)m->base_kd;
-  for (int f = 0; f < 3; f++) {
-    int ip = 1 + f * NL;
-    d->f[MF_tsel][ip] = 2; d->f[MF_kp][ip] = (T)m->kp[0]; d->f[MF_kd][ip] = (T)m->kd[0];
-    d->f[MF_tsel][ip + 1] = 3; d->f[MF_kp][ip + 1] = (T)m->kp[1]; d->f[MF_kd][ip + 1] = (T)m->kd[1];
-  }
-  d->f[MF_tsel][B - 1] = 4; d->f[MF_kp][B - 1] = (T)m->kp[2]; d->f[MF_kd][B - 1] = (T)m->kd[2];
+  auto set_pd = [&](int body, int tsel, double kp, double kd) {
+    int sl[3]; const int ns = slots(body, sl);
+    for (int r = 0; r < ns; r++) { d->f[MF_tsel][sl[r]] = (T)tsel; d->f[MF_kp][sl[r]] = (T)kp; d->f[MF_kd][sl[r]] = (T)kd; }
+  };
+  set_pd(0, 1, m->base_kp, m->base_kd);
+  for (int f = 0; f < 3; f++) { set_pd(1 + f * NL, 2, m->kp[0], m->kd[0]); set_pd(2 + f * NL, 3, m->kp[1], m->kd[1]); }
+  set_pd(B - 1, 4, m->kp[2], m->kd[2]);
   // geoms: first geom of a body is its primary, a second one (the hook plate) goes to the h* slot
   for (int g = 0; g < m->ngeom; g++) {
-    int b = m->g_body[g];
+    if (m->g_body[g] <= 0 || m->g_body[g] >= B) FAIL("collision geom on the base or outside the gripper");
+    int sl[3]; slots(m->g_body[g], sl);
+    const int b = sl[0];
     double R[9]; quat2mat_h(m->g_quat[g], R);
     int base = (d->f[MF_gtype][b] < 0) ? MF_gtype : ((d->f[MF_htype][b] < 0) ? MF_htype : -1);
     if (base < 0) FAIL("more than two collision geoms on one body");
@@ -433,7 +290,11 @@ static int build_model(const GmjModel* m, DevModel<T>* d) {
   d->ground_friction = (T)m->ground_friction; d->finger_length = (T)m->finger_length; d->segment_length = (T)m->segment_length;
   d->EI = (T)m->EI; d->clearance = (T)m->fingertip_clearance;
   d->hook_length = (T)m->hook_length; d->hook_angle_deg = (T)m->hook_angle_deg; d->finger_width = (T)m->finger_width;
-  for (int f = 0; f < 3; f++) { d->tip_lane[f] = m->tip_body[f]; d->finger_lane[f] = m->finger_body[f]; for (int k = 0; k < 9; k++) d->tip_mat[f][k] = (T)m->tip_mat[f][k]; }
+  for (int f = 0; f < 3; f++) {
+    int sl[3]; slots(m->tip_body[f], sl); d->tip_lane[f] = sl[0];
+    slots(m->finger_body[f], sl); d->finger_lane[f] = sl[0];
+    for (int k = 0; k < 9; k++) d->tip_mat[f][k] = (T)m->tip_mat[f][k];
+  }
   return 0;
 }
 
@@ -487,33 +348,27 @@ static int build_settings(const GmjSettings* s, DevSettings* d) {
 }
 
 // ------------------------------------------------------------------------------------------ C ABI
-template <typename T, int N>
-static int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
-                          float* reward, uint8_t* done, float* events, cudaStream_t st) {
-  const bool combined = (flags & STEP_COMBINED) != 0;
-  constexpr int WPB = StepCfg<T, N>::WPB;
-  size_t smem = sizeof(WarpShared<T, N>) * WPB;
-  static bool attr_set = false;
-  if (!attr_set) { CK(cudaFuncSetAttribute(k_step<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
-  int blocks = (h->n_envs + WPB - 1) / WPB;
-  constexpr int LW = GMJ_LIFT_WPB < WPB ? GMJ_LIFT_WPB : WPB;
-  if (flags & STEP_LIST) blocks = (h->n_envs + LW - 1) / LW;
-  const int list_blocks = combined ? (h->n_envs + LW - 1) / LW : 0;   // worst case every env owes a lift; empty list blocks exit at once
-  k_step<T, N><<<blocks + list_blocks, 32 * WPB, smem, st>>>((EnvState<T>*)h->envs, (const DevModel<T>*)h->model, h->settings,
-      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks, h->perm, h->hist);
-  CK(cudaGetLastError());
-  h->smem_bytes = smem;
-  return 0;
-}
+// step-kernel instantiations live in their own translation units (gmj_inst.cu)
+#define GMJ_DECL_NARROW(T, N) extern template int launch_step_TN<T, N>(GmjHandle*, int, int, const int32_t*, const float*, float*, float*, uint8_t*, float*, cudaStream_t)
+#define GMJ_DECL_WIDE(T, N) extern template int launch_step_wide_TN<T, N>(GmjHandle*, int, int, const int32_t*, const float*, float*, float*, uint8_t*, float*, cudaStream_t)
+GMJ_DECL_NARROW(float, 5); GMJ_DECL_NARROW(float, 8); GMJ_DECL_NARROW(double, 5); GMJ_DECL_NARROW(double, 8);
+GMJ_DECL_WIDE(float, 16); GMJ_DECL_WIDE(float, 24); GMJ_DECL_WIDE(double, 16); GMJ_DECL_WIDE(double, 24);
+
+// run `...` with T = the handle's physics type and QC = its state capacity
+#define GMJ_FOR_STATE(h, ...) do { \
+    if (!(h)->wide) { if ((h)->precision == 0) { using T = float; constexpr int QC = 40; __VA_ARGS__; } else { using T = double; constexpr int QC = 40; __VA_ARGS__; } } \
+    else { if ((h)->precision == 0) { using T = float; constexpr int QC = GMJ_WQC; __VA_ARGS__; } else { using T = double; constexpr int QC = GMJ_WQC; __VA_ARGS__; } } \
+  } while (0)
+
 template <typename T>
 static int launch_step_T(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
                          float* reward, uint8_t* done, float* events, cudaStream_t st) {
   switch (h->N) {
     case 5: return launch_step_TN<T, 5>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
-#ifndef GMJ_ONLY_F5            // development switch: compile one instantiation only
     case 8: return launch_step_TN<T, 8>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
-#endif
-    default: FAIL("this build instantiates the step kernel for N = 5 and N = 8 segments only");
+    case 16: return launch_step_wide_TN<T, 16>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
+    case 24: return launch_step_wide_TN<T, 24>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
+    default: FAIL("this build instantiates the step kernel for N = 5, 8 (one env per warp) and N = 16, 24 (one env per block) segments");
   }
 }
 static int launch_step(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
@@ -522,13 +377,22 @@ static int launch_step(GmjHandle* h, int flags, int nsub, const int32_t* actions
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   if (h->precision == 0) return launch_step_T<float>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
-#ifndef GMJ_ONLY_F5
   return launch_step_T<double>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
-#else
-  FAIL("built with GMJ_ONLY_F5");
-#endif
 }
-static size_t env_bytes(const GmjHandle* h) { return h->precision == 0 ? sizeof(EnvState<float>) : sizeof(EnvState<double>); }
+static size_t env_bytes(const GmjHandle* h) { size_t n = 0; GMJ_FOR_STATE(h, n = sizeof(EnvState<T, QC>)); return n; }
+
+template <typename T, int LN>
+static int upload_model(GmjHandle* h, const GmjModel* model) {
+  DevModel<T, LN>* dm = new DevModel<T, LN>();
+  if (build_model<T, LN>(model, dm)) { delete dm; return 1; }
+  DevModel<T, LN>* dev = nullptr;
+  cudaError_t e = cudaMalloc(&dev, sizeof(*dm));
+  if (e == cudaSuccess) e = cudaMemcpy(dev, dm, sizeof(*dm), cudaMemcpyHostToDevice);
+  delete dm;
+  if (e != cudaSuccess) { gmj_set_error(std::string("model upload: ") + cudaGetErrorString(e)); return 1; }
+  h->model = dev; h->model_s = static_cast<const DevModelS<T>*>(dev);
+  return 0;
+}
 
 extern "C" {
 
@@ -549,16 +413,14 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) FAIL("no CUDA device: libgripper_b200 has no CPU fallback");
   CK(cudaSetDevice(device));
   GmjHandle* h = new GmjHandle();
-  memset(h, 0, sizeof(*h));
+  memset((void*)h, 0, sizeof(*h));
   h->n_envs = n_envs; h->device = device; h->precision = precision; h->N = model->N; h->B = model->B; h->hm = *model;
   h->env_id_offset = env_id_offset;
-  if (precision == 0) {
-    DevModel<float> dm; if (build_model<float>(model, &dm)) { delete h; return 1; }
-    CK(cudaMalloc(&h->model, sizeof(dm))); CK(cudaMemcpy(h->model, &dm, sizeof(dm), cudaMemcpyHostToDevice));
-  } else {
-    DevModel<double> dm; if (build_model<double>(model, &dm)) { delete h; return 1; }
-    CK(cudaMalloc(&h->model, sizeof(dm))); CK(cudaMemcpy(h->model, &dm, sizeof(dm), cudaMemcpyHostToDevice));
-  }
+  h->wide = model->B > 32;
+  int rc;
+  if (!h->wide) rc = precision == 0 ? upload_model<float, 32>(h, model) : upload_model<double, 32>(h, model);
+  else rc = precision == 0 ? upload_model<float, GMJ_WNT>(h, model) : upload_model<double, GMJ_WNT>(h, model);
+  if (rc) { delete h; return 1; }
   CK(cudaMalloc(&h->envs, env_bytes(h) * (size_t)n_envs));
   CK(cudaMemset(h->envs, 0, env_bytes(h) * (size_t)n_envs));
   CK(cudaMalloc(&h->settings, sizeof(DevSettings)));
@@ -597,8 +459,7 @@ int gmj_reset(GmjHandle* h, const uint8_t* mask_dev, void* stream) {
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
-  if (h->precision == 0) k_reset<float><<<nb, tb, 0, st>>>((EnvState<float>*)h->envs, (const DevModel<float>*)h->model, h->settings, h->n_envs, mask_dev, h->env_id_offset);
-  else k_reset<double><<<nb, tb, 0, st>>>((EnvState<double>*)h->envs, (const DevModel<double>*)h->model, h->settings, h->n_envs, mask_dev, h->env_id_offset);
+  GMJ_FOR_STATE(h, k_reset<T, QC><<<nb, tb, 0, st>>>((EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->settings, h->n_envs, mask_dev, h->env_id_offset));
   CK(cudaGetLastError());
   return 0;
 }
@@ -611,17 +472,14 @@ int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const 
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
-  if (h->precision == 0) k_spawn<float><<<nb, tb, 0, st>>>((EnvState<float>*)h->envs, (const DevModel<float>*)h->model, h->settings, h->objects, h->n_objects, h->n_envs, idx_dev, xyr_dev, mask_dev, xy_range, rot_range, h->err_flag);
-  else k_spawn<double><<<nb, tb, 0, st>>>((EnvState<double>*)h->envs, (const DevModel<double>*)h->model, h->settings, h->objects, h->n_objects, h->n_envs, idx_dev, xyr_dev, mask_dev, xy_range, rot_range, h->err_flag);
+  GMJ_FOR_STATE(h, k_spawn<T, QC><<<nb, tb, 0, st>>>((EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->settings, h->objects, h->n_objects, h->n_envs, idx_dev, xyr_dev, mask_dev, xy_range, rot_range, h->err_flag));
   CK(cudaGetLastError());
   return 0;
 }
 
-// set_action for every env, then the termination action's 2 x sim_steps_per_action lift substeps
-// (quirk Q8: they run INSIDE MjClass::set_action) on a compacted list of just those envs -- in the
-// lockstep kernel a single lifting env would otherwise hold its whole block for 3S substeps.
-// Pass 1: set_action for every env; envs that owe the termination action's 2 x sim_steps_per_action lift
-// substeps (quirk Q8: they run INSIDE MjClass::set_action) are recorded in env_list / pending_extra.
+// Narrow kernels, pass 1: set_action for every env; envs that owe the termination action's 2 x sim_steps_per_action
+// lift substeps (quirk Q8: they run INSIDE MjClass::set_action) are recorded in env_list / pending_extra, the
+// others are counting-sorted by expected load.
 static int launch_collect(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, void* stream) {
   CK(cudaSetDevice(h->device));
   CK(cudaMemsetAsync(h->env_count, 0, sizeof(int), (cudaStream_t)stream));
@@ -633,18 +491,22 @@ static int launch_collect(GmjHandle* h, const int32_t* actions_dev, const float*
   CK(cudaGetLastError());
   return 0;
 }
-// Fused step = pass 1 + ONE combined launch: the first blocks take the (few) lifting envs, densely packed,
-// and run lift + action substeps back to back; the other blocks take everybody else. In the lockstep
-// kernel a single lifting env would otherwise hold its whole block for 3S substeps.
+// Fused step. Narrow kernels: pass 1 + ONE combined launch: the first blocks take the (few) lifting envs, densely
+// packed, and run lift + action substeps back to back; the other blocks take everybody else (in the lockstep
+// kernel a single lifting env would otherwise hold its whole block for 3S substeps). Wide kernels: one launch,
+// blocks are independent so the lift substeps run inline.
 int gmj_step(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, float* obs_dev, float* reward_dev,
              uint8_t* done_dev, float* events_dev, void* stream) {
   if (!h || !actions_dev) FAIL("gmj_step: null handle or actions");
+  if (h->wide) return launch_step(h, STEP_SET_ACTION | STEP_SUBSTEPS | STEP_SENSORS | STEP_TAIL | STEP_OUTPUT, -1, actions_dev, frac_dev,
+                                  obs_dev, reward_dev, done_dev, events_dev, stream);
   if (launch_collect(h, actions_dev, frac_dev, stream)) return 1;
   return launch_step(h, STEP_SUBSTEPS | STEP_SENSORS | STEP_TAIL | STEP_OUTPUT | STEP_COMBINED, -1, nullptr, nullptr,
                      obs_dev, reward_dev, done_dev, events_dev, stream);
 }
 int gmj_set_action(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, void* stream) {
   if (!h || !actions_dev) FAIL("gmj_set_action: null handle or actions");
+  if (h->wide) return launch_step(h, STEP_SET_ACTION | STEP_SUBSTEPS | STEP_SENSORS, 0, actions_dev, frac_dev, nullptr, nullptr, nullptr, nullptr, stream);
   if (launch_collect(h, actions_dev, frac_dev, stream)) return 1;
   return launch_step(h, STEP_SUBSTEPS | STEP_SENSORS | STEP_LIST, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, stream);
 }
@@ -679,8 +541,7 @@ int gmj_get_state_host(GmjHandle* h, double* qpos_host, double* qvel_host) {
   size_t nq = (size_t)h->n_envs * (h->B + 7), nv = (size_t)h->n_envs * (h->B + 6);
   if (ensure_scratch(h, nq + nv)) return 1;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
-  if (h->precision == 0) k_dump<float><<<nb, tb>>>((const EnvState<float>*)h->envs, h->n_envs, h->B, h->scratch, h->scratch + nq, nullptr);
-  else k_dump<double><<<nb, tb>>>((const EnvState<double>*)h->envs, h->n_envs, h->B, h->scratch, h->scratch + nq, nullptr);
+  GMJ_FOR_STATE(h, k_dump<T, QC><<<nb, tb>>>((const EnvState<T, QC>*)h->envs, h->n_envs, h->B, h->scratch, h->scratch + nq, nullptr));
   CK(cudaGetLastError());
   if (qpos_host) CK(cudaMemcpy(qpos_host, h->scratch, nq * sizeof(double), cudaMemcpyDeviceToHost));
   if (qvel_host) CK(cudaMemcpy(qvel_host, h->scratch + nq, nv * sizeof(double), cudaMemcpyDeviceToHost));
@@ -693,15 +554,10 @@ int gmj_probe_host(GmjHandle* h, double* probe_host) {
   size_t n = (size_t)h->n_envs * GMJ_PROBE_LEN;
   if (ensure_scratch(h, n)) return 1;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
-  if (h->precision == 0) {
-    k_dump<float><<<nb, tb>>>((const EnvState<float>*)h->envs, h->n_envs, h->B, nullptr, nullptr, h->scratch);
-    if (h->N == 5) k_gauge<float, 5><<<nb, tb>>>((const EnvState<float>*)h->envs, (const DevModel<float>*)h->model, h->n_envs, h->scratch);
-    else if (h->N == 8) k_gauge<float, 8><<<nb, tb>>>((const EnvState<float>*)h->envs, (const DevModel<float>*)h->model, h->n_envs, h->scratch);
-  } else {
-    k_dump<double><<<nb, tb>>>((const EnvState<double>*)h->envs, h->n_envs, h->B, nullptr, nullptr, h->scratch);
-    if (h->N == 5) k_gauge<double, 5><<<nb, tb>>>((const EnvState<double>*)h->envs, (const DevModel<double>*)h->model, h->n_envs, h->scratch);
-    else if (h->N == 8) k_gauge<double, 8><<<nb, tb>>>((const EnvState<double>*)h->envs, (const DevModel<double>*)h->model, h->n_envs, h->scratch);
-  }
+  GMJ_FOR_STATE(h, k_dump<T, QC><<<nb, tb>>>((const EnvState<T, QC>*)h->envs, h->n_envs, h->B, nullptr, nullptr, h->scratch));
+#define GMJ_GAUGE(NN) GMJ_FOR_STATE(h, k_gauge<T, NN, QC><<<nb, tb>>>((const EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->n_envs, h->scratch))
+  switch (h->N) { case 5: GMJ_GAUGE(5); break; case 8: GMJ_GAUGE(8); break; case 16: GMJ_GAUGE(16); break; case 24: GMJ_GAUGE(24); break; default: break; }
+#undef GMJ_GAUGE
   CK(cudaGetLastError());
   CK(cudaMemcpy(probe_host, h->scratch, n * sizeof(double), cudaMemcpyDeviceToHost));
   return 0;
@@ -712,8 +568,7 @@ int gmj_stats(GmjHandle* h, GmjStats* out) {
   CK(cudaSetDevice(h->device));
   CK(cudaMemset(h->stats_dev, 0, 8 * sizeof(unsigned long long)));
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
-  if (h->precision == 0) k_stats<float><<<nb, tb>>>((const EnvState<float>*)h->envs, h->n_envs, h->stats_dev);
-  else k_stats<double><<<nb, tb>>>((const EnvState<double>*)h->envs, h->n_envs, h->stats_dev);
+  GMJ_FOR_STATE(h, k_stats<T, QC><<<nb, tb>>>((const EnvState<T, QC>*)h->envs, h->n_envs, h->stats_dev));
   CK(cudaGetLastError());
   unsigned long long v[8];
   CK(cudaMemcpy(v, h->stats_dev, sizeof(v), cudaMemcpyDeviceToHost));
@@ -729,8 +584,7 @@ int gmj_set_welds(GmjHandle* h, int mask_on, void* stream) {
   if (!h) FAIL("null handle");
   CK(cudaSetDevice(h->device));
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
-  if (h->precision == 0) k_set_welds<float><<<nb, tb, 0, (cudaStream_t)stream>>>((EnvState<float>*)h->envs, h->n_envs, h->B, h->N, mask_on);
-  else k_set_welds<double><<<nb, tb, 0, (cudaStream_t)stream>>>((EnvState<double>*)h->envs, h->n_envs, h->B, h->N, mask_on);
+  GMJ_FOR_STATE(h, k_set_welds<T, QC><<<nb, tb, 0, (cudaStream_t)stream>>>((EnvState<T, QC>*)h->envs, h->n_envs, h->B, h->N, mask_on));
   CK(cudaGetLastError());
   return 0;
 }

@@ -22,10 +22,12 @@
 struct DevGripper { double x, y, z, th; int sx, sy, sz, pad; };
 
 // per-env persistent state (one block per env in HBM)
-template <typename T>
+// QC = capacity of qpos/qvel: 40 for the lane-per-dof kernels (B <= 32), 96 for the wide kernels (B <= 88)
+template <typename T, int QC = 40>
 struct EnvState {
-  T qpos[40];                 // [0,B) gripper joints; [32,39) object pos(3)+quat(4)
-  T qvel[40];                 // [0,B) gripper; [32,38) object lin(3 world)+ang(3 body)
+  static constexpr int OQ = QC - 8;   // first object entry
+  T qpos[QC];                 // [0,B) gripper joints in reference dof order; [OQ,OQ+7) object pos(3)+quat(4)
+  T qvel[QC];                 // [0,B) gripper; [OQ,OQ+6) object lin(3 world)+ang(3 body)
   T fprev[GMJ_RMAX];          // PGS warm start
   T weld_anchor[8];           // joint value at weld activation (7 used)
   T obj[20];                  // type,size3,round,quat4,mass,inertia3,friction,z_rest,bbox3
@@ -68,14 +70,19 @@ enum {
 };
 
 template <typename T>
-struct DevModel {
-  T f[MF_COUNT][32];
+struct DevModelS {               // scalars (all the tail logic needs)
   int N, B, NL, palm_lane;
   T gravity, solref_tc, solref_dr, solimp[5];
   T ground_friction, finger_length, segment_length, EI, clearance, zref;
   T hook_length, hook_angle_deg, finger_width;
   int tip_lane[3], finger_lane[3];
   T tip_mat[3][9];
+  T qpos0[GMJ_MAXB];           // keyframe, reference dof order
+};
+// LN = 32: lane-per-dof kernels (lane == reference dof index); LN = 96: wide kernels, slot = 32 * finger + lane
+template <typename T, int LN = 32>
+struct DevModel : DevModelS<T> {
+  T f[MF_COUNT][LN];
 };
 
 struct DevSettings {
@@ -144,9 +151,9 @@ template <> __device__ __forceinline__ void sincosT<double>(double t, double* s,
 
 // Double-precision libm calls expand to hundreds of SASS instructions each; the step kernel runs at
 // the speed of instruction fetch, so every call site shares ONE out-of-line copy.
-__device__ __noinline__ double nd_asin(double x) { return asin(x); }
-__device__ __noinline__ double nd_sin(double x) { return sin(x); }
-__device__ __noinline__ double nd_cos(double x) { return cos(x); }
+static __device__ __noinline__ double nd_asin(double x) { return asin(x); }
+static __device__ __noinline__ double nd_sin(double x) { return sin(x); }
+static __device__ __noinline__ double nd_cos(double x) { return cos(x); }
 // round() (half away from zero), exact for |x| < 2^51: truncate, then step on the remainder. The libm
 // expansion is ~70 instructions; this is called three times per stepper tick.
 __device__ __forceinline__ double nd_round(double x) {
@@ -154,7 +161,7 @@ __device__ __forceinline__ double nd_round(double x) {
   if (d >= 0.5) r += 1.0; else if (d <= -0.5) r -= 1.0;
   return r;
 }
-__device__ __noinline__ double nd_log(double x) { return log(x); }
+static __device__ __noinline__ double nd_log(double x) { return log(x); }
 template <typename T> __device__ __forceinline__ T sqrtT(T x);
 template <> __device__ __forceinline__ float sqrtT<float>(float x) {
   // MUFU.RSQ + one Newton step (<= 1 ulp), no out-of-line slow path: sqrtf() is ~12 instructions per site

@@ -16,18 +16,18 @@
 #include "gmj_collide.cuh"
 #include "gmj_tail.cuh"
 
-template <typename T, int N>
+template <typename T, int N, int QC = 40>
 struct WarpShared {
   static constexpr int B = 3 * N + 8;
   static constexpr int NW = B + 6;          // whitened row: B gripper columns (lane order) + 6 object columns
   static constexpr int WS = NW | 1;         // odd stride: conflict-free when lanes walk rows
-  EnvState<T> e;
+  EnvState<T, QC> e;
   WarpAux<T> ax;
   T W[GMJ_RMAX + 1][WS];            // whitened rows; row nrow holds the whitened smooth force
   T A[GMJ_RMAX * (GMJ_RMAX + 1) / 2]; // packed lower triangle of W W^T, overwritten by its Cholesky factor
   T u[WS + 1];                      // W^T f scratch of the LCP solver
   T L2[3][N + 2][N + 3];            // second factor, for column access in the back substitution
-  T qfk[40];                        // qpos of the last kinematics pass (weld anchors)
+  T qfk[QC];                        // qpos of the last kinematics pass (weld anchors)
   T rpos[GMJ_RMAX], rjv[GMJ_RMAX], rmu[GMJ_RMAX];
   int rtype[GMJ_RMAX], rfirst[GMJ_RMAX], rlane[GMJ_RMAX];
 };
@@ -229,12 +229,12 @@ __device__ __forceinline__ T jac_entry(const Topo<N>& tp, int bl, V3<T> p, V3<T>
 // Entry-parallel: the nr (nr + 1) / 2 packed entries are dealt 32 at a time, lane e computes
 // A[i][j] = W_i . W_j for its entry (W_i is a broadcast or near-broadcast read, W_j walks rows with an odd
 // stride). bcol (optional, per owned row lane / lane + 32) = W_r . W[nr], the extra column of the dual.
-template <typename T, int N>
-__device__ void form_A(WarpShared<T, N>& ws, int nr, int lane, T* bcol) {
-  constexpr int NW = WarpShared<T, N>::NW;
+template <typename T, int N, int NT = 32, int QC>
+__device__ void form_A(WarpShared<T, N, QC>& ws, int nr, int lane, T* bcol) {   // lane in [0, NT): NT threads share the entries
+  constexpr int NW = WarpShared<T, N, QC>::NW;
   const int ne = nr * (nr + 1) / 2;
 #pragma unroll 1
-  for (int e0 = 0; e0 < ne; e0 += 32) {
+  for (int e0 = 0; e0 < ne; e0 += NT) {
     const int e = e0 + lane;
     const bool ok = e < ne;
     const int ee = ok ? e : 0;
@@ -274,9 +274,9 @@ __device__ void form_A(WarpShared<T, N>& ws, int nr, int lane, T* bcol) {
 // reached) and gets w on the inactive rows from W (w = W (W^T f) + b). A second round has to rebuild
 // A from W first; with the warm-started active set that happens in about 1 % of the substeps.
 // Lane owns rows lane and lane + 32; b, R, type, f are per owned row. Returns the number of rounds.
-template <typename T, int N>
-__device__ int lcp_solve(WarpShared<T, N>& ws, int nr, int lane, const T* b, const T* R, const int* type, T* f, bool warm) {
-  constexpr int NW = WarpShared<T, N>::NW;
+template <typename T, int N, int QC>
+__device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b, const T* R, const int* type, T* f, bool warm) {
+  constexpr int NW = WarpShared<T, N, QC>::NW;
   T* A = ws.A;
   const T eps = sizeof(T) == 8 ? T(1e-12) : T(2e-6);
   const int maxit = 40;

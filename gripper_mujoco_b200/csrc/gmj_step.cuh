@@ -1,0 +1,274 @@
+// gmj_step.cuh -- the step kernels and their launchers. Each (precision, N) instantiation is compiled in its own
+// translation unit (gmj_inst.cu with -DINST_T / -DINST_N [/ -DINST_WIDE]) so the build runs in parallel.
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/gmj.h"
+#include "gmj_wide.cuh"
+
+// environments (warps) per block of the FP32 step kernel, one block per SM: as many as shared memory
+// holds (N = 5: 12 x 16.1 KB, 14 measured no faster, N = 8: 12 x 18.8 KB of the 227 KB)
+// envs are dealt to blocks in order of expected load so that the warps of a lockstep block finish each
+// phase together (ncu: stall_barrier was the top stall with arrival order)
+#ifndef GMJ_LIFT_WPB
+#define GMJ_LIFT_WPB 12
+#endif
+#define GMJ_SORT_BUCKETS 16
+#define GMJ_SORT_DIV 3
+#ifndef GMJ_BLOCKS_PER_SM
+#define GMJ_BLOCKS_PER_SM 1
+#endif
+#ifndef GMJ_WPB_F32_N5
+#define GMJ_WPB_F32_N5 12
+#endif
+#ifndef GMJ_WPB_F32_N8
+#define GMJ_WPB_F32_N8 12
+#endif
+
+void gmj_set_error(const std::string& msg);      // gmj_api.cu (thread-local last error)
+#define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) { gmj_set_error(std::string(#x) + ": " + cudaGetErrorString(_e)); return 1; } } while (0)
+#define FAIL(msg) do { gmj_set_error(msg); return 1; } while (0)
+
+struct GmjHandle {
+  int n_envs, device, precision, N, B;
+  int wide;              // 1: B > 32, one env per 96-thread block (gmj_wide.cuh), state EnvState<T, 96>, model DevModel<T, 96>
+  const void* model_s;   // the DevModelS<T> base of *model
+  uint32_t env_id_offset;
+  void* envs;            // EnvState<T>[n_envs]
+  void* model;           // DevModel<T>
+  DevSettings* settings; // device
+  DevSettings hs;        // host copy
+  GmjObject* objects; int n_objects;
+  int* err_flag;
+  int* env_list; int* env_count;   // envs that owe the 2S termination-lift substeps this step
+  int* perm; int* hist;            // load-sorted order of the other envs; hist[0..16) counts, hist[16..32) cursors
+  unsigned long long* stats_dev;
+  double* scratch; size_t scratch_len;
+  GmjModel hm;
+  size_t smem_bytes;
+};
+
+// ------------------------------------------------------------------------------------------ kernels
+enum { STEP_SET_ACTION = 1, STEP_SUBSTEPS = 2, STEP_TAIL = 4, STEP_OUTPUT = 8, STEP_SENSORS = 16,
+       STEP_COLLECT = 32,   // set_action only: append envs that owe extra substeps (termination lift) to env_list
+       STEP_LIST = 64,      // run on the envs of env_list[0 .. *env_count) instead of all envs
+       STEP_COMBINED = 128 }; // blocks [0, list_blocks) take env_list (owed lift substeps first), the rest all other envs
+
+template <typename T> __device__ __forceinline__ void copy_words(void* dst, const void* src, int nbytes, int lane) {
+  const uint32_t* s = (const uint32_t*)src; uint32_t* d = (uint32_t*)dst;
+  for (int i = lane; i < nbytes / 4; i += 32) d[i] = s[i];
+}
+
+// One warp per environment, WPB environments per block. flags select the phases so the same kernel
+// serves gmj_step (all), gmj_set_action, gmj_action_step, gmj_substeps and gmj_observe.
+// The kernel is instruction-fetch bound (ncu: stall_no_inst dominates, the step is ~25 k SASS
+// instructions of mostly straight-line code against a 32 KB L1.5 I-cache), so the warps of a block
+// are kept in lockstep with a block barrier per substep: one fetch stream then feeds WPB warps.
+template <typename T, int N> struct StepCfg { static constexpr int WPB = sizeof(T) == 4 ? (N <= 5 ? GMJ_WPB_F32_N5 : GMJ_WPB_F32_N8) : 4; };
+
+template <typename T, int N>
+__global__ void __launch_bounds__(32 * StepCfg<T, N>::WPB, GMJ_BLOCKS_PER_SM)
+k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const DevSettings* __restrict__ Sp, int n_envs,
+       int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
+       float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,
+       int* __restrict__ err_flag, int* __restrict__ env_list, int* __restrict__ env_count, int list_blocks,
+       const int* __restrict__ perm, int* __restrict__ hist) {
+  constexpr int WPB = StepCfg<T, N>::WPB;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int s_nsub_max;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int bid = blockIdx.x;
+  bool list_block = (flags & STEP_LIST) != 0;
+  if (flags & STEP_COMBINED) { list_block = bid < list_blocks; if (!list_block) bid -= list_blocks; }
+  int env = bid * WPB + warp;
+  bool valid = env < n_envs;
+  if (list_block) {                        // the collected envs, GMJ_LIFT_WPB per block; surplus blocks leave at once
+    // a lifting env runs 3S substeps back to back: few warps per block keep that critical path short
+    // (a 4-warp block steps ~2.5x faster than a full one), the idle warps only pass the barriers
+    constexpr int LW = GMJ_LIFT_WPB < WPB ? GMJ_LIFT_WPB : WPB;
+    const int cnt = *env_count;
+    if (bid * LW >= cnt) return;
+    env = bid * LW + warp;
+    valid = warp < LW && env < cnt;
+    env = valid ? env_list[env] : 0;
+  } else if (flags & STEP_COMBINED) {      // everybody else, in the load-sorted order built by k_sort_scatter
+    const int n_rest = n_envs - *env_count;
+    if (bid * WPB >= n_rest) return;
+    valid = env < n_rest;
+    env = valid ? perm[env] : 0;
+  }
+  WarpShared<T, N>& ws = *reinterpret_cast<WarpShared<T, N>*>(smem_raw + (size_t)warp * sizeof(WarpShared<T, N>));
+  const DevModel<T>& M = *Mp; const DevSettings& S = *Sp;
+  if (threadIdx.x == 0) s_nsub_max = 0;
+  if (valid) {
+    copy_words<T>(&ws.e, &envs[env], sizeof(EnvState<T>), lane);
+    if (lane == 0) { ws.ax.ncon = 0; ws.ax.nrow = 0; ws.ax.niter = 0; ws.ax.wrist_z = ws.e.wrist_z; }
+    ws.qfk[lane] = ws.e.qpos[lane];
+  }
+  __syncthreads();
+  EnvState<T>& e = ws.e;
+  int extra = 0;
+  if ((flags & STEP_SET_ACTION) && valid) {
+    if (lane == 0) {
+      extra = set_action<T>(e, S, M, actions[env], frac ? frac[env] : 0.0f);
+      if (extra < 0) { extra = 0; if (err_flag) atomicExch(err_flag, 1); }
+    }
+    if ((flags & STEP_COLLECT) && lane == 0) {
+      e.pending_extra = extra;
+      if (extra > 0) env_list[atomicAdd(env_count, 1)] = env;
+      else {                               // load key: constraint rows of the last substep (contacts dominate the cost)
+        int key = e.nrow_prev / GMJ_SORT_DIV; if (key >= GMJ_SORT_BUCKETS) key = GMJ_SORT_BUCKETS - 1;
+        e.sort_key = key; atomicAdd(&hist[key], 1);
+      }
+    }
+    extra = __shfl_sync(GMJ_FULL, extra, 0);
+    __syncwarp();
+  }
+  if (list_block && valid) {               // owed lift substeps run first, exactly as inside MjClass::set_action
+    extra = (int)e.pending_extra;
+    __syncwarp();
+    if (lane == 0) e.pending_extra = 0;
+  }
+  if (flags & STEP_SUBSTEPS) {
+    const int nsub = valid ? extra + (nsub_override >= 0 ? nsub_override : (int)S.s.general[GS_sim_steps_per_action]) : 0;
+    if (lane == 0) atomicMax(&s_nsub_max, nsub);
+    __syncthreads();
+    const int nsub_max = s_nsub_max;
+    const double dtd = S.s.general[GS_mujoco_timestep];
+    const bool curve = S.s.general[GS_curve_validation] != 0;
+    const T tipf = curve ? (T)S.s.general[GS_tip_force_applied] : T(0);
+    for (int i = 0; i < nsub_max; i++) {
+      __syncthreads();                       // lockstep: shared instruction stream
+      if (i < nsub) {
+        if (curve && lane == 0) for (int id = 0; id < 6; id++) set_weld<T, N>(e, id, 1, ws.qfk);   // apply_segment_force re-locks every step
+        __syncwarp();
+        physics_substep<T, N, 32 * WPB>(ws, M, S, lane, dtd, tipf);
+        phase_barrier<32 * WPB>(GMJ_NPHASE);
+        if (lane == 0) update_all<T, N>(e, ws.qfk);
+        __syncwarp();
+        if (flags & STEP_SENSORS) monitor_sensors<T, N>(e, S, M, ws.ax, lane);
+        __syncwarp();
+      } else { phase_idle<32 * WPB>(); phase_barrier<32 * WPB>(GMJ_NPHASE); }
+    }
+    if (valid && lane == 0) e.wrist_z = (float)ws.ax.wrist_z;
+  }
+  if (!valid) return;
+  if ((flags & STEP_TAIL) && lane == 0) {
+    sense_gripper_state<T>(e, S, M);
+    update_env<T>(e, S, ws.ax);
+    e.num_action_steps += 1;
+  }
+  if ((flags & STEP_OUTPUT) && lane == 0) {
+    if (reward) { float r = calc_reward<T>(e, S); e.last_reward = r; reward[env] = r; }
+    int d = calc_done<T>(e, S); e.last_done = d;
+    if (done) done[env] = (uint8_t)d;
+    if (obs) get_observation<T>(e, S, obs + (size_t)env * S.n_obs);
+    if (events) event_state<T>(e, events + (size_t)env * GMJ_EVENT_STATE_LEN);
+  }
+  __syncwarp();
+  copy_words<T>(&envs[env], &ws.e, sizeof(EnvState<T>), lane);
+}
+
+template <typename T, int N>
+int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
+                          float* reward, uint8_t* done, float* events, cudaStream_t st) {
+  const bool combined = (flags & STEP_COMBINED) != 0;
+  constexpr int WPB = StepCfg<T, N>::WPB;
+  size_t smem = sizeof(WarpShared<T, N>) * WPB;
+  static bool attr_set = false;
+  if (!attr_set) { CK(cudaFuncSetAttribute(k_step<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
+  int blocks = (h->n_envs + WPB - 1) / WPB;
+  constexpr int LW = GMJ_LIFT_WPB < WPB ? GMJ_LIFT_WPB : WPB;
+  if (flags & STEP_LIST) blocks = (h->n_envs + LW - 1) / LW;
+  const int list_blocks = combined ? (h->n_envs + LW - 1) / LW : 0;   // worst case every env owes a lift; empty list blocks exit at once
+  k_step<T, N><<<blocks + list_blocks, 32 * WPB, smem, st>>>((EnvState<T>*)h->envs, (const DevModel<T>*)h->model, h->settings,
+      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks, h->perm, h->hist);
+  CK(cudaGetLastError());
+  h->smem_bytes = smem;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ wide kernel
+// One environment per 96-thread block (gmj_wide.cuh). The termination action's 2S lift substeps (quirk Q8:
+// they run INSIDE MjClass::set_action) are executed inline, before the S substeps of the action.
+template <typename T, int N>
+__global__ void __launch_bounds__(GMJ_WNT)
+k_step_wide(EnvState<T, GMJ_WQC>* __restrict__ envs, const DevModel<T, GMJ_WNT>* __restrict__ Mp, const DevSettings* __restrict__ Sp,
+            int n_envs, int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
+            float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,
+            int* __restrict__ err_flag) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WideShared<T, N>& ws = *reinterpret_cast<WideShared<T, N>*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int env = blockIdx.x;
+  if (env >= n_envs) return;
+  const DevModel<T, GMJ_WNT>& M = *Mp; const DevSettings& S = *Sp;
+  {
+    const uint32_t* s = (const uint32_t*)&envs[env]; uint32_t* d = (uint32_t*)&ws.e;
+    for (int i = tid; i < (int)(sizeof(EnvState<T, GMJ_WQC>) / 4); i += GMJ_WNT) d[i] = s[i];
+  }
+  __syncthreads();
+  EnvState<T, GMJ_WQC>& e = ws.e;
+  if (tid == 0) { ws.ax.ncon = 0; ws.ax.nrow = 0; ws.ax.niter = 0; ws.ax.wrist_z = e.wrist_z; ws.extra = 0; }
+  for (int i = tid; i < GMJ_WQC; i += GMJ_WNT) ws.qfk[i] = e.qpos[i];
+  __syncthreads();
+  if (flags & STEP_SET_ACTION) {
+    if (tid == 0) {
+      int extra = set_action<T>(e, S, M, actions[env], frac ? frac[env] : 0.0f);
+      if (extra < 0) { extra = 0; if (err_flag) atomicExch(err_flag, 1); }
+      ws.extra = extra;
+    }
+    __syncthreads();
+  }
+  if (flags & STEP_SUBSTEPS) {
+    const int nsub = ws.extra + (nsub_override >= 0 ? nsub_override : (int)S.s.general[GS_sim_steps_per_action]);
+    const double dtd = S.s.general[GS_mujoco_timestep];
+    const bool curve = S.s.general[GS_curve_validation] != 0;
+    const T tipf = curve ? (T)S.s.general[GS_tip_force_applied] : T(0);
+    for (int i = 0; i < nsub; i++) {
+      if (curve && tid == 0) for (int id = 0; id < 6; id++) set_weld<T, N>(e, id, 1, ws.qfk);   // apply_segment_force re-locks every step
+      __syncthreads();
+      physics_substep_wide<T, N>(ws, M, S, tid, dtd, tipf);
+      __syncthreads();
+      if (tid == 0) update_all<T, N>(e, ws.qfk);
+      __syncthreads();
+      if ((flags & STEP_SENSORS) && warp == 0) monitor_sensors<T, N>(e, S, M, ws.ax, lane);
+      __syncthreads();
+    }
+    if (tid == 0) e.wrist_z = (float)ws.ax.wrist_z;
+  }
+  if ((flags & STEP_TAIL) && tid == 0) {
+    sense_gripper_state<T>(e, S, M);
+    update_env<T>(e, S, ws.ax);
+    e.num_action_steps += 1;
+  }
+  if ((flags & STEP_OUTPUT) && tid == 0) {
+    if (reward) { float r = calc_reward<T>(e, S); e.last_reward = r; reward[env] = r; }
+    int d = calc_done<T>(e, S); e.last_done = d;
+    if (done) done[env] = (uint8_t)d;
+    if (obs) get_observation<T>(e, S, obs + (size_t)env * S.n_obs);
+    if (events) event_state<T>(e, events + (size_t)env * GMJ_EVENT_STATE_LEN);
+  }
+  __syncthreads();
+  {
+    uint32_t* d = (uint32_t*)&envs[env]; const uint32_t* s = (const uint32_t*)&ws.e;
+    for (int i = tid; i < (int)(sizeof(EnvState<T, GMJ_WQC>) / 4); i += GMJ_WNT) d[i] = s[i];
+  }
+}
+
+template <typename T, int N>
+int launch_step_wide_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
+                        float* reward, uint8_t* done, float* events, cudaStream_t st) {
+  size_t smem = sizeof(WideShared<T, N>);
+  static bool attr_set = false;
+  if (!attr_set) { CK(cudaFuncSetAttribute(k_step_wide<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
+  k_step_wide<T, N><<<h->n_envs, GMJ_WNT, smem, st>>>((EnvState<T, GMJ_WQC>*)h->envs, (const DevModel<T, GMJ_WNT>*)h->model, h->settings,
+      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag);
+  CK(cudaGetLastError());
+  h->smem_bytes = smem;
+  return 0;
+}

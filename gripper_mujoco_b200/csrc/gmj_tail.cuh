@@ -90,20 +90,20 @@ __device__ inline void g_step_to(DevGripper& g, const DevGripper& t, int num) { 
 // ------------------------------------------------------------------ windows (src/slidingwindow.h:9-55)
 enum { ST_gauge = 0, ST_axial = 3, ST_palm = 6, ST_wristz = 7, ST_motor = 8, ST_basexy = 11, ST_basez = 13,
        ST_yaw = 14, ST_cart = 15 };
-template <typename T> __device__ __forceinline__ void win_add(EnvState<T>& e, int s, float v) {
+template <typename T, int QC> __device__ __forceinline__ void win_add(EnvState<T, QC>& e, int s, float v) {
   int i = e.win_i[s] + 1;
   if (i > GMJ_WIN - 1) i = 0;
   e.win_i[s] = i; e.win[s][i] = v;
 }
-template <typename T> __device__ __forceinline__ float win_read(const EnvState<T>& e, int s, int n) {
+template <typename T, int QC> __device__ __forceinline__ float win_read(const EnvState<T, QC>& e, int s, int n) {
   int idx = e.win_i[s] - n;
   while (idx < 0) idx += GMJ_WIN;
   return e.win[s][idx];
 }
 
 // samplers MjType::Sensor::*_sample (src/mjclass.h:278-453)
-template <typename T>
-__device__ inline int sample_stream(const EnvState<T>& e, int st, int mode, int p, int r, float* out) {
+template <typename T, int QC>
+__device__ inline int sample_stream(const EnvState<T, QC>& e, int st, int mode, int p, int r, float* out) {
   int Tn = 1 + r * p;
   if (mode == GSM_raw) {
     int n = Tn - 1;
@@ -141,7 +141,7 @@ __device__ inline int sample_stream(const EnvState<T>& e, int st, int mode, int 
 }
 
 // ------------------------------------------------------------------ sensors
-template <typename T> __device__ __noinline__ float dev_uniform(EnvState<T>& e, const DevSettings& S) {
+template <typename T, int QC> __device__ __noinline__ float dev_uniform(EnvState<T, QC>& e, const DevSettings& S) {
   uint64_t seed = (uint64_t)S.s.general[GS_random_seed];
   uint32_t x = philox_first(e.rng_ctr++, e.env_id, 0, 0, (uint32_t)seed, (uint32_t)(seed >> 32));
   return (float)(x >> 8) * (1.0f / 16777216.0f);
@@ -154,8 +154,8 @@ __device__ inline float apply_normalisation(const double* sn, float value) {    
   if (value < -normalise) return -1.0f;
   return value / normalise;
 }
-template <typename T>
-__device__ inline float apply_noise(EnvState<T>& e, const DevSettings& S, int sensor, float value, int i) { // src/mjclass.h:176-223
+template <typename T, int QC>
+__device__ inline float apply_noise(EnvState<T, QC>& e, const DevSettings& S, int sensor, float value, int i) { // src/mjclass.h:176-223
   const double* sn = S.s.sensor[sensor];
   if (!sn[GSF_use_noise] || !S.s.general[GS_use_noise_seeded]) return value;
   const float eps = 1.1920929e-07f;
@@ -175,7 +175,7 @@ __device__ inline float apply_noise(EnvState<T>& e, const DevSettings& S, int se
   if (value > 1) value = 1; else if (value < -1) value = -1;
   return value;
 }
-template <typename T> __device__ inline int ready_to_read(EnvState<T>& e, const DevSettings& S, int sensor, int slot) { // src/mjclass.h:225-241
+template <typename T, int QC> __device__ inline int ready_to_read(EnvState<T, QC>& e, const DevSettings& S, int sensor, int slot) { // src/mjclass.h:225-241
   float rr = (float)S.s.sensor[sensor][GSF_read_rate];
   double between = 1 / rr;
   if (e.time > e.last_read_time[slot] + between) { e.last_read_time[slot] = e.time; return 1; }
@@ -184,8 +184,8 @@ template <typename T> __device__ inline int ready_to_read(EnvState<T>& e, const 
 
 // luke::read_armadillo_gauge (src/myfunctions.cpp:2699-2795): cubic least squares through the
 // N+1 joint positions of one finger evaluated at 50 mm, in mm. FP64 (arma::polyfit is double).
-template <typename T, int N>
-__device__ inline float read_gauge(const EnvState<T>& e, const DevModel<T>& M, int finger) {
+template <typename T, int N, int QC>
+__device__ inline float read_gauge(const EnvState<T, QC>& e, const DevModelS<T>& M, int finger) {
   double L = (double)M.segment_length;
   double X[N + 1][4], y[N + 1], fx[N + 1];
   double cum = 0; fx[0] = 0; y[0] = 0;
@@ -238,8 +238,8 @@ struct DevForces {
   double obj_f[3][3], obj_palm[3], obj_gnd[3], all_f[3][3], all_palm[3], gnd_f[3][3];
   double obj_f_loc[3][3], obj_palm_loc[3], all_f_loc[3][3], all_palm_loc[3], gnd_f_loc[3][3];
 };
-template <typename T>
-__device__ inline void extract_forces(const EnvState<T>& e, const WarpAux<T>& ax, DevForces& F) {
+template <typename T, int QC>
+__device__ inline void extract_forces(const EnvState<T, QC>& e, const WarpAux<T>& ax, DevForces& F) {
   double* z = (double*)&F;
   for (int k = 0; k < (int)(sizeof(DevForces) / sizeof(double)); k++) z[k] = 0;
   if (!e.has_object) return;
@@ -278,8 +278,8 @@ __device__ inline void extract_forces(const EnvState<T>& e, const WarpAux<T>& ax
 }
 
 // MjClass::monitor_sensors (src/mjclass.cpp:741-898)
-template <typename T, int N>
-__device__ inline void monitor_sensors(EnvState<T>& e, const DevSettings& S, const DevModel<T>& M, const WarpAux<T>& ax, int lane) {
+template <typename T, int N, int QC>
+__device__ inline void monitor_sensors(EnvState<T, QC>& e, const DevSettings& S, const DevModelS<T>& M, const WarpAux<T>& ax, int lane) {
   // warp-collective: lane 0 owns the sensor state, the three cubic gauge fits (FP64 QR) run on lanes 0-2
   const double* g = S.s.general;
   int due = 0;
@@ -331,8 +331,8 @@ __device__ inline void monitor_sensors(EnvState<T>& e, const DevSettings& S, con
 // Each weld joins two bodies connected by one 1-dof joint, so its anchor (relative pose at
 // activation, luke::set_constraint src/myfunctions.cpp:1177-1279) reduces to the joint value at
 // the pose of the last kinematics pass (`qfk`). Bits of weld_on: 0-2 pris, 3-5 rev, 6 palm.
-template <typename T, int N>
-__device__ inline void set_weld(EnvState<T>& e, int id, int on, const T* qfk) {
+template <typename T, int N, int QC>
+__device__ inline void set_weld(EnvState<T, QC>& e, int id, int on, const T* qfk) {
   if (on) {
     int j = (id < 3) ? (1 + id * (N + 2)) : ((id < 6) ? (2 + (id - 3) * (N + 2)) : (3 * N + 7));
     e.weld_anchor[id] = qfk[j];
@@ -341,8 +341,8 @@ __device__ inline void set_weld(EnvState<T>& e, int id, int on, const T* qfk) {
 }
 
 // luke::update_all (src/myfunctions.cpp:2110-2284) + apply_antiroll (src/objecthandler.cpp:1034-1059)
-template <typename T, int N>
-__device__ inline void update_all(EnvState<T>& e, const T* qfk) {
+template <typename T, int N, int QC>
+__device__ inline void update_all(EnvState<T, QC>& e, const T* qfk) {
   const double time_per_step = 10 / 2000.0;
   if (e.time > e.last_step_time + time_per_step) {
     // old_moving bit 3 ("steady"): the previous tick moved no motor, the stepper state was already the
@@ -368,15 +368,15 @@ __device__ inline void update_all(EnvState<T>& e, const T* qfk) {
     }
   }
   if (e.has_object) {
-    T vx = e.qvel[32], vy = e.qvel[33], vz = e.qvel[34];
+    T vx = e.qvel[QC - 8], vy = e.qvel[QC - 7], vz = e.qvel[QC - 6];
     if (sqrt((double)vx * vx + (double)vy * vy + (double)vz * vz) < 1e-6)
-      for (int k = 0; k < 6; k++) e.qvel[32 + k] = 0;
+      for (int k = 0; k < 6; k++) e.qvel[QC - 8 + k] = 0;
   }
 }
 
 // ------------------------------------------------------------------ set_action (src/mjclass.cpp:1528-1630)
-template <typename T>
-__device__ inline int clamp_base(EnvState<T>& e, const double* g) {
+template <typename T, int QC>
+__device__ inline int clamp_base(EnvState<T, QC>& e, const double* g) {
   int wl = 1;
   if (e.base_x > g[GS_base_x_max]) { e.base_x = g[GS_base_x_max]; wl = 0; }
   if (e.base_x < g[GS_base_x_min]) { e.base_x = g[GS_base_x_min]; wl = 0; }
@@ -386,8 +386,8 @@ __device__ inline int clamp_base(EnvState<T>& e, const double* g) {
   if (e.base_z < g[GS_base_z_min]) { e.base_z = g[GS_base_z_min]; wl = 0; }
   return wl;
 }
-template <typename T>
-__device__ inline int call_action(EnvState<T>& e, const DevSettings& S, int a, double v) { // src/mjclass.h:546-571
+template <typename T, int QC>
+__device__ inline int call_action(EnvState<T, QC>& e, const DevSettings& S, int a, double v) { // src/mjclass.h:546-571
   v *= (int)S.s.action[a][GAF_sign];
   DevGripper& t = e.tend;
   const double* g = S.s.general;
@@ -411,8 +411,8 @@ __device__ inline int call_action(EnvState<T>& e, const DevSettings& S, int a, d
 }
 // returns number of EXTRA substeps to burn before the action (termination lift, quirk Q8), or -1
 // for an out-of-range action
-template <typename T>
-__device__ inline int set_action(EnvState<T>& e, const DevSettings& S, const DevModel<T>& M, int action, float fraction) {
+template <typename T, int QC>
+__device__ inline int set_action(EnvState<T, QC>& e, const DevSettings& S, const DevModelS<T>& M, int action, float fraction) {
   int wl = 1, extra = 0;
   e.termination_sent = 0;
   if (action < 0 || action >= S.n_actions) return -1;
@@ -458,8 +458,8 @@ __device__ inline float normalise_between(float val, float mn, float mx) {  // s
   if (val > mx) return 1.0f; else if (val < mn) return -1.0f;
   return 2 * (val - mn) / (mx - mn) - 1;
 }
-template <typename T>
-__device__ inline void sense_gripper_state(EnvState<T>& e, const DevSettings& S, const DevModel<T>& M) {
+template <typename T, int QC>
+__device__ inline void sense_gripper_state(EnvState<T, QC>& e, const DevSettings& S, const DevModelS<T>& M) {
   const double* g = S.s.general;
   float sx = normalise_between((float)e.tend.x, (float)49e-3, (float)134e-3);
   float sy = normalise_between((float)e.tend.y, (float)49e-3, (float)134e-3);
@@ -517,8 +517,8 @@ __device__ inline float linear_reward(float val, float mn, float mx, float overs
   }
   return (val - mn) / (mx - mn);
 }
-template <typename T>
-__device__ inline void update_events(EnvState<T>& e, const DevSettings& S) {     // src/mjclass.cpp:5437-5469
+template <typename T, int QC>
+__device__ inline void update_events(EnvState<T, QC>& e, const DevSettings& S) {     // src/mjclass.cpp:5437-5469
   for (int k = 0; k < GBE_COUNT; k++) {
     int v = e.ev_value[k] != 0;
     e.ev_row[k] = e.ev_row[k] * v + v;
@@ -539,15 +539,15 @@ __device__ inline void update_events(EnvState<T>& e, const DevSettings& S) {    
 __device__ inline float mag3d(const double* v) { return (float)sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); }
 
 // MjClass::update_env (src/mjclass.cpp:966-1346), single live object
-template <typename T>
-__device__ inline void update_env(EnvState<T>& e, const DevSettings& S, const WarpAux<T>& ax) {
+template <typename T, int QC>
+__device__ inline void update_env(EnvState<T, QC>& e, const DevSettings& S, const WarpAux<T>& ax) {
   const double* g = S.s.general;
   const float ftol = 1e-5f;
   float* V = e.ev_value;
   if (!e.has_object) { V[GBE_step_num] = 1; update_events(e, S); return; }
   DevForces F;
   extract_forces(e, ax, F);
-  double qx = (double)e.qpos[32], qy = (double)e.qpos[33], qz = (double)e.qpos[34];
+  double qx = (double)e.qpos[QC - 8], qy = (double)e.qpos[QC - 7], qz = (double)e.qpos[QC - 6];
   double rx = qx - e.base_x, ry = qy - e.base_y;
   float distance = (float)sqrt(rx * rx + ry * ry);
   float f1 = mag3d(F.obj_f_loc[0]), f2 = mag3d(F.obj_f_loc[1]), f3 = mag3d(F.obj_f_loc[2]);
@@ -618,8 +618,8 @@ __device__ inline void update_env(EnvState<T>& e, const DevSettings& S, const Wa
 }
 
 // calc_rewards + MjClass::reward (src/mjclass.cpp:5471-5528, 3000-3049)
-template <typename T>
-__device__ inline float calc_reward(EnvState<T>& e, const DevSettings& S) {
+template <typename T, int QC>
+__device__ inline float calc_reward(EnvState<T, QC>& e, const DevSettings& S) {
   float reward = 0;
   for (int k = 0; k < GBE_COUNT; k++)
     if (e.ev_row[k] >= (int)S.s.binary[k][GBF_trigger]) reward += (float)S.s.binary[k][GBF_reward];
@@ -637,8 +637,8 @@ __device__ inline float calc_reward(EnvState<T>& e, const DevSettings& S) {
   return reward;
 }
 // MjClass::is_done (src/mjclass.cpp:1632-1698)
-template <typename T>
-__device__ inline int calc_done(const EnvState<T>& e, const DevSettings& S) {
+template <typename T, int QC>
+__device__ inline int calc_done(const EnvState<T, QC>& e, const DevSettings& S) {
   const float ftol = 1e-5f;
   if (e.unstable) return 1;
   for (int k = 0; k < GBE_COUNT; k++) { int d = (int)S.s.binary[k][GBF_done]; if (d && e.ev_row[k] >= d) return 1; }
@@ -650,15 +650,15 @@ __device__ inline int calc_done(const EnvState<T>& e, const DevSettings& S) {
   return 0;
 }
 // EventTrack::vectorise (src/mjclass.cpp:5594-5615)
-template <typename T>
-__device__ inline void event_state(const EnvState<T>& e, float* out) {
+template <typename T, int QC>
+__device__ inline void event_state(const EnvState<T, QC>& e, float* out) {
   int n = 0;
   for (int k = 0; k < GBE_COUNT; k++) out[n++] = (float)e.ev_row[k];
   for (int k = 0; k < GLE_COUNT; k++) { out[n++] = (float)e.ev_row[EVL(k)]; out[n++] = e.ev_last[EVL(k)]; }
 }
 // MjClass::get_observation (src/mjclass.cpp:1700-1959)
-template <typename T>
-__device__ inline int get_observation(const EnvState<T>& e, const DevSettings& S, float* obs) {
+template <typename T, int QC>
+__device__ inline int get_observation(const EnvState<T, QC>& e, const DevSettings& S, float* obs) {
   const GmjSettings& s = S.s;
   int n = 0;
   int smode = (int)s.general[GS_sensor_sample_mode], tmode = (int)s.general[GS_state_sample_mode];

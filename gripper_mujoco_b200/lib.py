@@ -14,7 +14,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GMJ_LIB: development override to A/B-test differently compiled builds of the same sources
 SO_PATH = os.environ.get("GMJ_LIB") or os.path.join(_HERE, "libgripper_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["gmj_api.cu", "gmj_physics.cuh", "gmj_tail.cuh", "gmj_collide.cuh", "gmj_device.cuh"]
+SOURCES = ["gmj_api.cu", "gmj_inst.cu", "gmj_step.cuh", "gmj_wide.cuh", "gmj_physics.cuh", "gmj_tail.cuh", "gmj_collide.cuh",
+           "gmj_device.cuh"]
 HEADERS = [os.path.join(_HERE, "..", "include", h) for h in ("gmj.h", "gmj_types.h")]
 
 GMJ_PROBE_LEN = 32
@@ -37,9 +38,26 @@ class GmjStats(C.Structure):
                 ("rows", C.c_int64), ("solver_iters", C.c_int64), ("contact_overflow", C.c_int64)]
 
 
-def nvcc_command(out: str = SO_PATH, extra: list[str] | None = None) -> list[str]:
-    return ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-            "-shared", "-Xcompiler", "-fPIC", *(extra or []), "-o", out, os.path.join(CSRC, "gmj_api.cu")]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
+# step-kernel instantiations, one translation unit each (compiled in parallel): (type, N, wide)
+INSTANCES = [("float", 5, False), ("float", 8, False), ("double", 5, False), ("double", 8, False),
+             ("float", 16, True), ("float", 24, True), ("double", 16, True), ("double", 24, True)]
+OBJ_DIR = os.path.join(_HERE, "..", "build", "obj")
+
+
+def nvcc_commands(out: str = SO_PATH, extra: list[str] | None = None, obj_dir: str = OBJ_DIR):
+    """(compile commands, link command): every command is a plain `nvcc` invocation for sm_100a."""
+    extra = list(extra or [])
+    objs, cmds = [], []
+    o = os.path.join(obj_dir, "gmj_api.o")
+    cmds.append(["nvcc", *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, "gmj_api.cu"), "-o", o]); objs.append(o)
+    for ty, n, wide in INSTANCES:
+        o = os.path.join(obj_dir, f"gmj_inst_{ty}_{n}.o")
+        cmds.append(["nvcc", *NVCC_FLAGS, *extra, f"-DINST_T={ty}", f"-DINST_N={n}", *(["-DINST_WIDE"] if wide else []),
+                     "-c", os.path.join(CSRC, "gmj_inst.cu"), "-o", o])
+        objs.append(o)
+    link = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", out, *objs]
+    return cmds, link
 
 
 def stale() -> bool:
@@ -50,12 +68,18 @@ def stale() -> bool:
     return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, out: str = SO_PATH, extra: list[str] | None = None) -> str:
     """Compile the CUDA extension for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
-    if force or stale():
-        cmd = nvcc_command(extra=["-Xptxas", "-v"] if verbose else None)
-        subprocess.check_call(cmd)
-    return SO_PATH
+    if force or out != SO_PATH or stale():
+        obj_dir = OBJ_DIR if out == SO_PATH else out + ".obj"
+        os.makedirs(obj_dir, exist_ok=True)
+        cmds, link = nvcc_commands(out, (extra or []) + (["-Xptxas", "-v"] if verbose else []), obj_dir)
+        procs = [subprocess.Popen(c) for c in cmds]
+        rcs = [p.wait() for p in procs]
+        if any(rcs):
+            raise subprocess.CalledProcessError(max(rcs), cmds[rcs.index(max(rcs))])
+        subprocess.check_call(link)
+    return out
 
 
 FMA_SO = os.path.join(_HERE, "libgmj_fma_peak.so")

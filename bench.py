@@ -133,7 +133,9 @@ def reference_arm(args):
 
 
 def workload_config(args, st):
-    return {"workload": f"configs[1]: {args.envs} envs/GPU, {args.segments}-segment fingers, set9_fullset-like 1750 objects, "
+    cfg = {(5, 4096): "configs[1]", (8, 16384): "configs[2]/[3] per-GPU shape", (24, 4096): "configs[4] sweep point"}.get(
+        (args.segments, args.envs), "custom")
+    return {"workload": f"{cfg}: {args.envs} envs/GPU, {args.segments}-segment fingers, set9_fullset-like 1750 objects, "
                         f"random discrete actions, auto-reset (cap {EPISODE_CAP})",
             "envs_per_gpu": args.envs, "segments": args.segments, "timestep": st.mujoco_timestep,
             "sim_steps_per_action": int(st.sim_steps_per_action), "noise": "on (Philox)",
@@ -304,9 +306,11 @@ def main():
     try:
         with open(os.path.join(ROOT, "profiles", "k_step_traffic.json")) as f:
             traffic = json.load(f).get("dram_bytes_per_launch")
+        if (args.segments, args.envs) != (5, 4096):       # the ncu capture is of the configs[1] launch only
+            traffic = None
     except Exception:  # noqa: BLE001
         pass
-    roofline = {"bound": "fp32", "kernel": f"k_step<float,{args.segments}>", "achieved": ach_tf, "peak": fp32_peak,
+    roofline = {"bound": "fp32", "kernel": (f"k_step<float,{args.segments}>" if args.segments <= 8 else f"k_step_wide<float,{args.segments}>"), "achieved": ach_tf, "peak": fp32_peak,
                 "unit": "TFLOP/s", "frac": ach_tf / fp32_peak, "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms": kern_ms, "flops_per_action_step": f_act, "mean_contacts_per_substep": nc,
                 "substeps_per_action_step": S_eff,

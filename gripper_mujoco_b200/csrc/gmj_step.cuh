@@ -196,7 +196,7 @@ int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, co
 // One environment per 96-thread block (gmj_wide.cuh). The termination action's 2S lift substeps (quirk Q8:
 // they run INSIDE MjClass::set_action) are executed inline, before the S substeps of the action.
 template <typename T, int N>
-__global__ void __launch_bounds__(GMJ_WNT)
+__global__ void __launch_bounds__(GMJ_WNT, sizeof(T) == 4 ? 4 : 1)
 k_step_wide(EnvState<T, GMJ_WQC>* __restrict__ envs, const DevModel<T, GMJ_WNT>* __restrict__ Mp, const DevSettings* __restrict__ Sp,
             int n_envs, int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
             float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,

@@ -43,6 +43,7 @@ struct WideShared : WarpShared<T, N, GMJ_WQC> {
   int cnt[2][4];                    // contacts per group: gripper-ground, gripper-object
   unsigned limmask[3];              // joint-limit violations per warp
   int ebad, extra;
+  alignas(32) T colb[3][2][32];     // per-warp column broadcast of the factorisation (double buffered)
 };
 
 // sum K per-thread partials over the whole environment (3 warps); every thread gets the same totals
@@ -95,29 +96,46 @@ __device__ __forceinline__ void fwd_w(WideShared<T, N>& ws, int& xn, const TopoW
   for (int m = 0; m < P; m++) pay[m] = sv[K + m];
 }
 
-// in-place LDL^T of one finger block (rows in shared memory, lane = row) + the base arrow.
-// In: Lw[i][k] = M[i][k] (k <= i), Mb = M[lane][base], dself = own diagonal of the palm / base lanes.
-// Out: Lw[i][k<i] = L, Lw[i][i] = pivot; D = pivot of this lane, lb = L[base][lane].
+// LDL^T of one finger block + the base arrow. The row of each lane stays in registers (fully unrolled right-looking
+// elimination); column k is published once per step through a per-warp shared buffer and read back by
+// broadcast, four entries per load.
+// In: row[k] = M[lane][k] (k <= lane), Mb = M[lane][base], dself = own diagonal of the palm / base lanes.
+// Out (shared): Lw[i][k<i] = L, Lw[i][i] = pivot; D = pivot of this lane, lb = L[base][lane].
+template <typename T> struct alignas(4 * sizeof(T)) Quad { T v[4]; };
 template <typename T, int N>
-__device__ void ldl_factor_w(WideShared<T, N>& ws, int& xn, const TopoW<N>& tp, T* Lw, T Mb, T dself, T& D, T& lb) {
+__device__ __forceinline__ void ldl_factor_w(WideShared<T, N>& ws, int& xn, const TopoW<N>& tp, const T (&rin)[N + 2], T* Lw, T Mb, T dself, T& D, T& lb) {
   constexpr int NL = N + 2, NLP = N + 3;
-#pragma unroll 1
+  T row[NL];
+#pragma unroll
+  for (int k = 0; k < NL; k++) row[k] = rin[k];
+#pragma unroll
   for (int k = 0; k < NL - 1; k++) {
-    const T inv = T(1) / Lw[k * NLP + k];
+    T* col = ws.colb[tp.w][k & 1];
+    col[tp.lane] = row[k];
+    __syncwarp();
+    const T inv = T(1) / col[k];
     const T Mbk = __shfl_sync(GMJ_FULL, Mb, k);
     const bool below = tp.chain && tp.local > k;
-    const T mk_pre = below ? Lw[tp.local * NLP + k] : T(0);
-    const T l = mk_pre * inv;
-    if (below) {
-      T* row = Lw + tp.local * NLP;
-      for (int j = k + 1; j <= tp.local; j++) row[j] -= l * Lw[j * NLP + k];
-      Mb -= (Mbk * inv) * mk_pre;
+    const T mk_pre = below ? row[k] : T(0);
+    const T l = mk_pre * inv;                       // 0 on the lanes that are not below the pivot: their rows stay
+#pragma unroll
+    for (int j4 = (k + 1) / 4; j4 < (NL + 3) / 4; j4++) {
+      const Quad<T> c = reinterpret_cast<const Quad<T>*>(col)[j4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int j = 4 * j4 + u;
+        if (j > k && j < NL) row[j] -= l * c.v[u];
+      }
     }
-    __syncwarp();
-    if (below) Lw[tp.local * NLP + k] = l;
-    __syncwarp();
+    Mb -= (Mbk * inv) * mk_pre;
+    if (below) row[k] = l;
   }
-  const T d = tp.chain ? Lw[tp.local * NLP + tp.local] : dself;
+  T d = dself;
+#pragma unroll
+  for (int k = 0; k < NL; k++) {
+    if (tp.chain && k <= tp.local) Lw[tp.local * NLP + k] = row[k];
+    if (tp.chain && k == tp.local) d = row[k];
+  }
   T s[1] = { (tp.chain || tp.palm) ? Mb * Mb / d : T(0) };
   xsum<T, N, 1>(ws, xn, tp.w, tp.lane, s);
   if (tp.base) { D = dself - s[0]; lb = 0; }
@@ -313,14 +331,12 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
   // mass matrix rows into the factor storage: M[lane][k] (k <= local), coupling to the base in Mb
   Sp<T> F = spimul(Ic, Sj);
   const T damp = tp.act ? M.f[MF_damp][tid] : T(0), stiff = tp.act ? M.f[MF_stiff][tid] : T(0);
-  if (tp.chain) {
-#pragma unroll 2
-    for (int k = 0; k <= tp.local; k++) {
-      const T* sk = ws.sj[32 * w + k];
-      T mv = sk[0] * F.w.x + sk[1] * F.w.y + sk[2] * F.w.z + sk[3] * F.v.x + sk[4] * F.v.y + sk[5] * F.v.z;
-      L1w[tp.local * NLP + k] = mv;
-      L2w[tp.local * NLP + k] = mv + (k == tp.local ? dt * damp : T(0));
-    }
+  T Mrow[NL];
+#pragma unroll
+  for (int k = 0; k < NL; k++) {
+    const T* sk = ws.sj[32 * w + k];
+    const T mv = sk[0] * F.w.x + sk[1] * F.w.y + sk[2] * F.w.z + sk[3] * F.v.x + sk[4] * F.v.y + sk[5] * F.v.z;
+    Mrow[k] = (tp.chain && k <= tp.local) ? mv : T(0);
   }
   Sp<T> Sb = spshfl(Sj, TW::BASE_L);
   const T Mb = (tp.chain || tp.palm) ? spdot(Sb, F) : T(0);
@@ -349,10 +365,11 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
   }
 
   // ------------------------------------------------------------------ factorisations
-  __syncwarp();
   T D, lb, D2, lb2;
-  ldl_factor_w<T, N>(ws, xn, tp, L1w, Mb, Mself, D, lb);
-  ldl_factor_w<T, N>(ws, xn, tp, L2w, Mb, Mself + dt * damp, D2, lb2);
+  ldl_factor_w<T, N>(ws, xn, tp, Mrow, L1w, Mb, Mself, D, lb);
+#pragma unroll
+  for (int k = 0; k < NL; k++) if (tp.chain && k == tp.local) Mrow[k] += dt * damp;
+  ldl_factor_w<T, N>(ws, xn, tp, Mrow, L2w, Mb, Mself + dt * damp, D2, lb2);
   const T rsq = tp.act ? T(1) / sqrtT<T>(D) : T(0);
   int bad = !(D > 0) && tp.act;
   // whitened smooth force w_s = D^-1/2 L^-1 tau

@@ -20,8 +20,8 @@ st = Settings()
 st.debug = False
 st.random_seed = 1234
 st.set_use_noise(True)
-st.mujoco_timestep, st.sim_steps_per_action = ({5: 7.02e-3, 8: 3.262e-3}[N], {5: 29, 8: 62}[N])
-st.bending_gauge.normalise = {5: 2.41, 8: 2.54}[N]
+st.mujoco_timestep, st.sim_steps_per_action = ({5: 7.02e-3, 8: 3.262e-3, 16: 1.039e-3, 24: 0.56e-3}[N], {5: 29, 8: 62, 16: 193, 24: 358}[N])
+st.bending_gauge.normalise = {5: 2.41, 8: 2.54, 16: 2.63, 24: 2.66}[N]
 st.wrist_sensor_Z.raw_value_offset = -23.3
 mj = MjClass(n, GripperParams(num_segments=N), settings=st, calibrate=False)
 mj.spawn_into_scene(0.01, float(np.pi / 2))

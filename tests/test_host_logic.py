@@ -86,10 +86,11 @@ def test_yield_load_formula():
 
 def test_calibration_flow_over_oracle():
     """find_highest_stable_timestep / auto sim steps / sensor calibration. The reference's thesis data
-    (max stable timestep 10.4 ms at N = 5, 4.3 ms at N = 8) is the sanity envelope for the restated
-    physics: +-10 %."""
+    (max stable timestep 10.4 ms at N = 5, 4.3 ms at N = 8, 1.299 ms at N = 16, 0.7 ms at N = 24:
+    rl/juypter/thesis_plots/mujoco_timesteps.csv, column t=0.9 w=28 inertia=50) is the sanity envelope for
+    the restated physics: +-10 %."""
     from oracle.calibrate import calibrated
-    for N, ref_max in [(5, 10.4e-3), (8, 4.3e-3)]:
+    for N, ref_max in [(5, 10.4e-3), (8, 4.3e-3), (16, 1.299e-3), (24, 0.7e-3)]:
         mdl, s, info = calibrated(GripperParams(num_segments=N))
         hi = info["highest_stable_timestep"]
         assert abs(hi / ref_max - 1) < 0.10

@@ -402,6 +402,7 @@ int gmj_set_settings(GmjHandle* h, const GmjSettings* settings) {
   if (!h || !settings) FAIL("null argument");
   CK(cudaSetDevice(h->device));
   if (build_settings(settings, &h->hs)) return 1;
+  { const char* t = getenv("GMJ_ASIN_TAB"); h->hs.asin_tab = (t && atoi(t) == 0) ? nullptr : h->asin_tab; }   // development switch
   CK(cudaMemcpy(h->settings, &h->hs, sizeof(DevSettings), cudaMemcpyHostToDevice));
   return 0;
 }
@@ -417,6 +418,12 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
   h->n_envs = n_envs; h->device = device; h->precision = precision; h->N = model->N; h->B = model->B; h->hm = *model;
   h->env_id_offset = env_id_offset;
   h->wide = model->B > 32;
+  {
+    int nsm = 0;
+    CK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device));
+    const char* bal = getenv("GMJ_BALANCE");                       // development switch: GMJ_BALANCE=0 launches full blocks
+    h->balance_sm = (bal && atoi(bal) == 0) ? 0 : nsm;
+  }
   int rc;
   if (!h->wide) rc = precision == 0 ? upload_model<float, 32>(h, model) : upload_model<double, 32>(h, model);
   else rc = precision == 0 ? upload_model<float, GMJ_WNT>(h, model) : upload_model<double, GMJ_WNT>(h, model);
@@ -424,6 +431,12 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
   CK(cudaMalloc(&h->envs, env_bytes(h) * (size_t)n_envs));
   CK(cudaMemset(h->envs, 0, env_bytes(h) * (size_t)n_envs));
   CK(cudaMalloc(&h->settings, sizeof(DevSettings)));
+  {                                    // finger angle of every leadscrew step difference (g_update_xy_steps, gmj_tail.cuh)
+    std::vector<double> tab(2 * G_TH_TAB + 1);
+    for (int d = -G_TH_TAB; d <= G_TH_TAB; d++) tab[d + G_TH_TAB] = asin((G_XY_STEP * d) / G_LEADSCREW);
+    CK(cudaMalloc(&h->asin_tab, tab.size() * sizeof(double)));
+    CK(cudaMemcpy(h->asin_tab, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice));
+  }
   CK(cudaMalloc(&h->err_flag, sizeof(int))); CK(cudaMemset(h->err_flag, 0, sizeof(int)));
   CK(cudaMalloc(&h->stats_dev, 8 * sizeof(unsigned long long)));
   CK(cudaMalloc(&h->env_list, sizeof(int) * (size_t)n_envs)); CK(cudaMalloc(&h->env_count, sizeof(int)));
@@ -437,7 +450,7 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
 int gmj_destroy(GmjHandle* h) {
   if (!h) return 0;
   cudaSetDevice(h->device);
-  cudaFree(h->envs); cudaFree(h->model); cudaFree(h->settings); cudaFree(h->err_flag); cudaFree(h->stats_dev); cudaFree(h->env_list); cudaFree(h->env_count); cudaFree(h->perm); cudaFree(h->hist);
+  cudaFree(h->envs); cudaFree(h->model); cudaFree(h->settings); cudaFree(h->err_flag); cudaFree(h->stats_dev); cudaFree(h->env_list); cudaFree(h->env_count); cudaFree(h->perm); cudaFree(h->hist); cudaFree(h->asin_tab);
   if (h->objects) cudaFree(h->objects);
   if (h->scratch) cudaFree(h->scratch);
   delete h;

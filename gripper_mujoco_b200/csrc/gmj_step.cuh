@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <string>
 #include <vector>
@@ -50,6 +51,8 @@ struct GmjHandle {
   double* scratch; size_t scratch_len;
   GmjModel hm;
   size_t smem_bytes;
+  double* asin_tab;      // device table for the stepper (DevSettings::asin_tab)
+  int balance_sm;        // SM count when the combined launch balances envs per block over the SMs, 0 = full blocks
 };
 
 // ------------------------------------------------------------------------------------------ kernels
@@ -76,7 +79,7 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
        int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
        float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,
        int* __restrict__ err_flag, int* __restrict__ env_list, int* __restrict__ env_count, int list_blocks,
-       const int* __restrict__ perm, int* __restrict__ hist) {
+       const int* __restrict__ perm, int* __restrict__ hist, int bal_sm) {
   constexpr int WPB = StepCfg<T, N>::WPB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_nsub_max;
@@ -96,9 +99,18 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
     valid = warp < LW && env < cnt;
     env = valid ? env_list[env] : 0;
   } else if (flags & STEP_COMBINED) {      // everybody else, in the load-sorted order built by k_sort_scatter
-    const int n_rest = n_envs - *env_count;
-    if (bid * WPB >= n_rest) return;
-    valid = env < n_rest;
+    // envs per block: the fewest full rounds over the SMs, then an equal share per block, so the last round is
+    // not a handful of full blocks on a few SMs (4096 envs / 12 = 2.3 rounds of 148 blocks). Lifting envs weigh 3.
+    const int cnt = *env_count, n_rest = n_envs - cnt;
+    int W = WPB;
+    if (bal_sm > 0) {
+      const int units = n_rest + 3 * cnt, rounds = (units + bal_sm * WPB - 1) / (bal_sm * WPB);
+      W = (units + bal_sm * rounds - 1) / (bal_sm * rounds);
+      W = W < 1 ? 1 : (W > WPB ? WPB : W);
+    }
+    if (bid * W >= n_rest) return;
+    env = bid * W + warp;
+    valid = warp < W && env < n_rest;
     env = valid ? perm[env] : 0;
   }
   WarpShared<T, N>& ws = *reinterpret_cast<WarpShared<T, N>*>(smem_raw + (size_t)warp * sizeof(WarpShared<T, N>));
@@ -148,7 +160,7 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
         __syncwarp();
         physics_substep<T, N, 32 * WPB>(ws, M, S, lane, dtd, tipf);
         phase_barrier<32 * WPB>(GMJ_NPHASE);
-        if (lane == 0) update_all<T, N>(e, ws.qfk);
+        if (lane == 0) update_all<T, N>(e, ws.qfk, S.asin_tab);
         __syncwarp();
         if (flags & STEP_SENSORS) monitor_sensors<T, N>(e, S, M, ws.ax, lane);
         __syncwarp();
@@ -185,8 +197,10 @@ int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, co
   constexpr int LW = GMJ_LIFT_WPB < WPB ? GMJ_LIFT_WPB : WPB;
   if (flags & STEP_LIST) blocks = (h->n_envs + LW - 1) / LW;
   const int list_blocks = combined ? (h->n_envs + LW - 1) / LW : 0;   // worst case every env owes a lift; empty list blocks exit at once
+  const int bal_sm = combined ? h->balance_sm : 0;
+  if (bal_sm > 0) blocks = bal_sm * ((3 * h->n_envs + bal_sm * WPB - 1) / (bal_sm * WPB));   // bound (every env lifting); surplus blocks exit at once
   k_step<T, N><<<blocks + list_blocks, 32 * WPB, smem, st>>>((EnvState<T>*)h->envs, (const DevModel<T>*)h->model, h->settings,
-      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks, h->perm, h->hist);
+      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks, h->perm, h->hist, bal_sm);
   CK(cudaGetLastError());
   h->smem_bytes = smem;
   return 0;
@@ -234,7 +248,7 @@ k_step_wide(EnvState<T, GMJ_WQC>* __restrict__ envs, const DevModel<T, GMJ_WNT>*
       __syncthreads();
       physics_substep_wide<T, N>(ws, M, S, tid, dtd, tipf);
       __syncthreads();
-      if (tid == 0) update_all<T, N>(e, ws.qfk);
+      if (tid == 0) update_all<T, N>(e, ws.qfk, S.asin_tab);
       __syncthreads();
       if ((flags & STEP_SENSORS) && warp == 0) monitor_sensors<T, N>(e, S, M, ws.ax, lane);
       __syncthreads();

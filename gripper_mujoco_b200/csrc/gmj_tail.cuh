@@ -28,13 +28,17 @@ struct WarpAux {                 // per-warp scratch written by the physics each
 #define G_LIMIT_TOL 1e-4
 #define G_XY_STEP (4.0 / (1.0 * 400 * 1e3))
 #define G_Z_STEP (4.8768 / (1 * 400 * 1e3))
+#define G_TH_TAB 2400                    // |sx - sy| <= 2250 at the +-40 degree limit
 #define G_XY_HOME (G_XY_MAX - 1.0 * (4 * 1e-3 / 1.0))
 #define G_Z_HOME (0.0 + 1.0 * (4.8768 * 1e-3 / 1))
 
 __device__ __forceinline__ double g_calc_th(double x, double y) { return nd_asin((y - x) / G_LEADSCREW); }
 __device__ __forceinline__ double g_calc_y(double x, double th) { return x + G_LEADSCREW * nd_sin(th); }
 
-__device__ inline int g_update_xy(DevGripper& g) {                    // gripper.cpp:6-90
+// tab != nullptr: x and y were just set from the integer step counts (g_step_to) whose difference is d; when no
+// limit moved them the angle comes from the table asin(G_XY_STEP d / G_LEADSCREW) -- the same value to the last
+// bit or two (x and y are rounded images of the lattice) without ~100 FP64 instructions on one lane.
+__device__ inline int g_update_xy(DevGripper& g, const double* tab = nullptr, int d = 0) {   // gripper.cpp:6-90
   int wl = 1;
   const double to_rad = 3.14159265358979323846 / 180.0;
   const double th_min = -40 * to_rad, th_max = 40 * to_rad;
@@ -42,7 +46,7 @@ __device__ inline int g_update_xy(DevGripper& g) {                    // gripper
   if (g.x < G_XY_MIN - G_LIMIT_TOL) { g.x = G_XY_MIN; wl = 0; }
   if (g.y > G_XY_MAX + G_LIMIT_TOL) { g.y = G_XY_MAX; wl = 0; }
   if (g.y < G_XY_MIN - G_LIMIT_TOL) { g.y = G_XY_MIN; wl = 0; }
-  double nth = g_calc_th(g.x, g.y);
+  double nth = (tab && wl && d >= -G_TH_TAB && d <= G_TH_TAB) ? __ldg(tab + d + G_TH_TAB) : g_calc_th(g.x, g.y);
   if (nth > th_max) { nth = th_max; g.y = g_calc_y(g.x, th_max); wl = 0; }
   if (nth < th_min) { nth = th_min; g.y = g_calc_y(g.x, th_min); wl = 0; }
   g.th = nth;
@@ -77,12 +81,12 @@ __device__ inline int g_set_xyz_m_rad(DevGripper& g, double x, double th, double
   return g_update_z(g) ? in_lim : 0;
 }
 __device__ inline void g_reset(DevGripper& g) { g_set_xyz_m(g, G_XY_HOME, G_XY_HOME, G_Z_HOME); }
-__device__ inline void g_step_to(DevGripper& g, const DevGripper& t, int num) { // gripper.cpp:158-228
+__device__ inline void g_step_to(DevGripper& g, const DevGripper& t, int num, const double* tab = nullptr) { // gripper.cpp:158-228
   int d[3] = { t.sx - g.sx, t.sy - g.sy, t.sz - g.sz };
 #pragma unroll
   for (int k = 0; k < 3; k++) { if (d[k] < -num) d[k] = -num; if (d[k] > num) d[k] = num; }
   g.x = G_XY_MAX - G_XY_STEP * (g.sx + d[0]); g.y = G_XY_MAX - G_XY_STEP * (g.sy + d[1]);
-  g_update_xy(g);
+  g_update_xy(g, tab, (g.sx + d[0]) - (g.sy + d[1]));
   g.z = G_Z_STEP * (g.sz + d[2]);
   g_update_z(g);
 }
@@ -342,7 +346,7 @@ __device__ inline void set_weld(EnvState<T, QC>& e, int id, int on, const T* qfk
 
 // luke::update_all (src/myfunctions.cpp:2110-2284) + apply_antiroll (src/objecthandler.cpp:1034-1059)
 template <typename T, int N, int QC>
-__device__ inline void update_all(EnvState<T, QC>& e, const T* qfk) {
+__device__ inline void update_all(EnvState<T, QC>& e, const T* qfk, const double* asin_tab) {
   const double time_per_step = 10 / 2000.0;
   if (e.time > e.last_step_time + time_per_step) {
     // old_moving bit 3 ("steady"): the previous tick moved no motor, the stepper state was already the
@@ -353,8 +357,10 @@ __device__ inline void update_all(EnvState<T, QC>& e, const T* qfk) {
     else {
       int nx = e.tend.sx != e.tnext.sx;
       int nz = e.tend.sz != e.tnext.sz;
-      double a = (180.0 / 3.14159265358979323846) * g_calc_th(e.tend.x, e.tend.y);
-      double b = (180.0 / 3.14159265358979323846) * g_calc_th(e.tnext.x, e.tnext.y);
+      // Target::revolute_moving compares calc_th of both targets; .th holds exactly that (g_update_xy), or the
+      // limit angle where y was clamped to it (equal within an ulp, the 0.5 degree test is 30 steps wide)
+      double a = (180.0 / 3.14159265358979323846) * e.tend.th;
+      double b = (180.0 / 3.14159265358979323846) * e.tnext.th;
       int ny = !(fabs(a - b) < 5e-1);
       int ox = e.old_moving & 1, oy = (e.old_moving >> 1) & 1, oz = (e.old_moving >> 2) & 1;
       if (nx != ox) for (int i = 0; i < 3; i++) set_weld<T, N>(e, i, !nx, qfk);
@@ -364,7 +370,7 @@ __device__ inline void update_all(EnvState<T, QC>& e, const T* qfk) {
       const int was_canon = (e.old_moving >> 4) & 1;
       e.old_moving = nx | (ny << 1) | (nz << 2) | ((nomove && was_canon) ? 8 : 0) | 16;
       e.last_step_time = e.time;
-      g_step_to(e.tnext, e.tend, 10);
+      g_step_to(e.tnext, e.tend, 10, asin_tab);
     }
   }
   if (e.has_object) {

@@ -6,8 +6,8 @@ static thread_local std::string g_err;
 void gmj_set_error(const std::string& msg) { g_err = msg; }
 
 // counting-sort scatter of the envs that owe no lift substeps: perm[offset(key) + slot] = env
-template <typename T>
-__global__ void k_sort_scatter(const EnvState<T>* __restrict__ envs, int n_envs, const int* __restrict__ hist,
+template <typename T, int QC>
+__global__ void k_sort_scatter(const EnvState<T, QC>* __restrict__ envs, int n_envs, const int* __restrict__ hist,
                                int* __restrict__ cursor, int* __restrict__ perm) {
   int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= n_envs) return;
@@ -490,7 +490,7 @@ int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const 
   return 0;
 }
 
-// Narrow kernels, pass 1: set_action for every env; envs that owe the termination action's 2 x sim_steps_per_action
+// Pass 1: set_action for every env; envs that owe the termination action's 2 x sim_steps_per_action
 // lift substeps (quirk Q8: they run INSIDE MjClass::set_action) are recorded in env_list / pending_extra, the
 // others are counting-sorted by expected load.
 static int launch_collect(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, void* stream) {
@@ -499,27 +499,22 @@ static int launch_collect(GmjHandle* h, const int32_t* actions_dev, const float*
   CK(cudaMemsetAsync(h->hist, 0, sizeof(int) * 2 * GMJ_SORT_BUCKETS, (cudaStream_t)stream));
   if (launch_step(h, STEP_SET_ACTION | STEP_COLLECT, 0, actions_dev, frac_dev, nullptr, nullptr, nullptr, nullptr, stream)) return 1;
   int tb = 256, nb = (h->n_envs + tb - 1) / tb;
-  if (h->precision == 0) k_sort_scatter<float><<<nb, tb, 0, (cudaStream_t)stream>>>((const EnvState<float>*)h->envs, h->n_envs, h->hist, h->hist + GMJ_SORT_BUCKETS, h->perm);
-  else k_sort_scatter<double><<<nb, tb, 0, (cudaStream_t)stream>>>((const EnvState<double>*)h->envs, h->n_envs, h->hist, h->hist + GMJ_SORT_BUCKETS, h->perm);
+  GMJ_FOR_STATE(h, k_sort_scatter<T, QC><<<nb, tb, 0, (cudaStream_t)stream>>>((const EnvState<T, QC>*)h->envs, h->n_envs, h->hist, h->hist + GMJ_SORT_BUCKETS, h->perm));
   CK(cudaGetLastError());
   return 0;
 }
-// Fused step. Narrow kernels: pass 1 + ONE combined launch: the first blocks take the (few) lifting envs, densely
-// packed, and run lift + action substeps back to back; the other blocks take everybody else (in the lockstep
-// kernel a single lifting env would otherwise hold its whole block for 3S substeps). Wide kernels: one launch,
-// blocks are independent so the lift substeps run inline.
+// Fused step: pass 1 + ONE combined launch: the first blocks take the (few) lifting envs, densely packed, and run
+// lift + action substeps back to back; the other blocks take everybody else (in a lockstep block a single lifting
+// env would otherwise hold the whole block for 3S substeps). Same scheme for the lane-per-dof and the wide kernels.
 int gmj_step(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, float* obs_dev, float* reward_dev,
              uint8_t* done_dev, float* events_dev, void* stream) {
   if (!h || !actions_dev) FAIL("gmj_step: null handle or actions");
-  if (h->wide) return launch_step(h, STEP_SET_ACTION | STEP_SUBSTEPS | STEP_SENSORS | STEP_TAIL | STEP_OUTPUT, -1, actions_dev, frac_dev,
-                                  obs_dev, reward_dev, done_dev, events_dev, stream);
   if (launch_collect(h, actions_dev, frac_dev, stream)) return 1;
   return launch_step(h, STEP_SUBSTEPS | STEP_SENSORS | STEP_TAIL | STEP_OUTPUT | STEP_COMBINED, -1, nullptr, nullptr,
                      obs_dev, reward_dev, done_dev, events_dev, stream);
 }
 int gmj_set_action(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, void* stream) {
   if (!h || !actions_dev) FAIL("gmj_set_action: null handle or actions");
-  if (h->wide) return launch_step(h, STEP_SET_ACTION | STEP_SUBSTEPS | STEP_SENSORS, 0, actions_dev, frac_dev, nullptr, nullptr, nullptr, nullptr, stream);
   if (launch_collect(h, actions_dev, frac_dev, stream)) return 1;
   return launch_step(h, STEP_SUBSTEPS | STEP_SENSORS | STEP_LIST, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, stream);
 }

@@ -207,54 +207,92 @@ int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, co
 }
 
 // ------------------------------------------------------------------------------------------ wide kernel
-// One environment per 96-thread block (gmj_wide.cuh). The termination action's 2S lift substeps (quirk Q8:
-// they run INSIDE MjClass::set_action) are executed inline, before the S substeps of the action.
+// 96 threads per environment (gmj_wide.cuh), WideCfg::EPB environments per block in lockstep (FP32: 4 at N = 24, one
+// block per SM; FP64: 1). Same two-pass scheme as the lane-per-dof kernel: pass 1 = set_action + collect (envs that
+// owe the termination action's 2S lift substeps -- quirk Q8, they run INSIDE MjClass::set_action -- go to env_list,
+// the others are counting-sorted by load), pass 2 = combined launch, the lifting envs densely packed in the first
+// blocks (a single lifter would hold its lockstep block for 3S substeps).
 template <typename T, int N>
-__global__ void __launch_bounds__(GMJ_WNT, sizeof(T) == 4 ? 4 : 1)
+__global__ void __launch_bounds__(GMJ_WNT * WideCfg<T, N>::EPB, 1)
 k_step_wide(EnvState<T, GMJ_WQC>* __restrict__ envs, const DevModel<T, GMJ_WNT>* __restrict__ Mp, const DevSettings* __restrict__ Sp,
             int n_envs, int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
             float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,
-            int* __restrict__ err_flag) {
+            int* __restrict__ err_flag, int* __restrict__ env_list, int* __restrict__ env_count, int list_blocks,
+            const int* __restrict__ perm, int* __restrict__ hist) {
+  constexpr int EPB = WideCfg<T, N>::EPB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  WideShared<T, N>& ws = *reinterpret_cast<WideShared<T, N>*>(smem_raw);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int env = blockIdx.x;
-  if (env >= n_envs) return;
+  __shared__ int s_nsub_max;
+  const int grp = threadIdx.x / GMJ_WNT, tid = threadIdx.x - grp * GMJ_WNT, lane = tid & 31, warp = tid >> 5;
+  WideShared<T, N>& ws = *reinterpret_cast<WideShared<T, N>*>(smem_raw + (size_t)grp * sizeof(WideShared<T, N>));
+  int bid = blockIdx.x;
+  bool list_block = (flags & STEP_LIST) != 0;
+  if (flags & STEP_COMBINED) { list_block = bid < list_blocks; if (!list_block) bid -= list_blocks; }
+  int env = bid * EPB + grp;
+  bool valid = env < n_envs;
+  if (list_block) {
+    const int cnt = *env_count;
+    if (bid * EPB >= cnt) return;
+    valid = env < cnt;
+    env = valid ? env_list[env] : 0;
+  } else if (flags & STEP_COMBINED) {
+    const int n_rest = n_envs - *env_count;
+    if (bid * EPB >= n_rest) return;
+    valid = env < n_rest;
+    env = valid ? perm[env] : 0;
+  } else if (bid * EPB >= n_envs) return;
   const DevModel<T, GMJ_WNT>& M = *Mp; const DevSettings& S = *Sp;
-  {
+  if (threadIdx.x == 0) s_nsub_max = 0;
+  if (tid == 0) ws.grp = grp;
+  if (valid) {
     const uint32_t* s = (const uint32_t*)&envs[env]; uint32_t* d = (uint32_t*)&ws.e;
     for (int i = tid; i < (int)(sizeof(EnvState<T, GMJ_WQC>) / 4); i += GMJ_WNT) d[i] = s[i];
   }
   __syncthreads();
   EnvState<T, GMJ_WQC>& e = ws.e;
-  if (tid == 0) { ws.ax.ncon = 0; ws.ax.nrow = 0; ws.ax.niter = 0; ws.ax.wrist_z = e.wrist_z; ws.extra = 0; }
-  for (int i = tid; i < GMJ_WQC; i += GMJ_WNT) ws.qfk[i] = e.qpos[i];
-  __syncthreads();
-  if (flags & STEP_SET_ACTION) {
-    if (tid == 0) {
-      int extra = set_action<T>(e, S, M, actions[env], frac ? frac[env] : 0.0f);
-      if (extra < 0) { extra = 0; if (err_flag) atomicExch(err_flag, 1); }
-      ws.extra = extra;
-    }
-    __syncthreads();
+  if (valid) {
+    if (tid == 0) { ws.ax.ncon = 0; ws.ax.nrow = 0; ws.ax.niter = 0; ws.ax.wrist_z = e.wrist_z; ws.extra = 0; }
+    for (int i = tid; i < GMJ_WQC; i += GMJ_WNT) ws.qfk[i] = e.qpos[i];
   }
+  __syncthreads();
+  if ((flags & STEP_SET_ACTION) && valid && tid == 0) {
+    int extra = set_action<T>(e, S, M, actions[env], frac ? frac[env] : 0.0f);
+    if (extra < 0) { extra = 0; if (err_flag) atomicExch(err_flag, 1); }
+    ws.extra = extra;
+    if (flags & STEP_COLLECT) {
+      e.pending_extra = extra;
+      if (extra > 0) env_list[atomicAdd(env_count, 1)] = env;
+      else {
+        int key = e.nrow_prev / GMJ_SORT_DIV; if (key >= GMJ_SORT_BUCKETS) key = GMJ_SORT_BUCKETS - 1;
+        e.sort_key = key; atomicAdd(&hist[key], 1);
+      }
+    }
+  }
+  if (list_block && valid && tid == 0) { ws.extra = (int)e.pending_extra; e.pending_extra = 0; }
+  __syncthreads();
   if (flags & STEP_SUBSTEPS) {
-    const int nsub = ws.extra + (nsub_override >= 0 ? nsub_override : (int)S.s.general[GS_sim_steps_per_action]);
+    const int nsub = valid ? ws.extra + (nsub_override >= 0 ? nsub_override : (int)S.s.general[GS_sim_steps_per_action]) : 0;
+    if (tid == 0) atomicMax(&s_nsub_max, nsub);
+    __syncthreads();
+    const int nsub_max = s_nsub_max;
     const double dtd = S.s.general[GS_mujoco_timestep];
     const bool curve = S.s.general[GS_curve_validation] != 0;
     const T tipf = curve ? (T)S.s.general[GS_tip_force_applied] : T(0);
-    for (int i = 0; i < nsub; i++) {
-      if (curve && tid == 0) for (int id = 0; id < 6; id++) set_weld<T, N>(e, id, 1, ws.qfk);   // apply_segment_force re-locks every step
-      __syncthreads();
-      physics_substep_wide<T, N>(ws, M, S, tid, dtd, tipf);
-      __syncthreads();
-      if (tid == 0) update_all<T, N>(e, ws.qfk, S.asin_tab);
-      __syncthreads();
-      if ((flags & STEP_SENSORS) && warp == 0) monitor_sensors<T, N>(e, S, M, ws.ax, lane);
-      __syncthreads();
+    for (int i = 0; i < nsub_max; i++) {
+      wide_phase<T, N>();                    // lockstep: one instruction stream for the EPB envs of the block
+      if (i < nsub) {
+        if (curve && tid == 0) for (int id = 0; id < 6; id++) set_weld<T, N>(e, id, 1, ws.qfk);   // apply_segment_force re-locks every step
+        env_sync<T, N>(ws);
+        physics_substep_wide<T, N>(ws, M, S, tid, dtd, tipf);
+        env_sync<T, N>(ws);
+        if (tid == 0) update_all<T, N>(e, ws.qfk, S.asin_tab);
+        env_sync<T, N>(ws);
+        if ((flags & STEP_SENSORS) && warp == 0) monitor_sensors<T, N>(e, S, M, ws.ax, lane);
+        env_sync<T, N>(ws);
+      } else wide_phase_idle<T, N>();
     }
-    if (tid == 0) e.wrist_z = (float)ws.ax.wrist_z;
+    if (valid && tid == 0) e.wrist_z = (float)ws.ax.wrist_z;
   }
+  if (!valid) return;
   if ((flags & STEP_TAIL) && tid == 0) {
     sense_gripper_state<T>(e, S, M);
     update_env<T>(e, S, ws.ax);
@@ -267,7 +305,7 @@ k_step_wide(EnvState<T, GMJ_WQC>* __restrict__ envs, const DevModel<T, GMJ_WNT>*
     if (obs) get_observation<T>(e, S, obs + (size_t)env * S.n_obs);
     if (events) event_state<T>(e, events + (size_t)env * GMJ_EVENT_STATE_LEN);
   }
-  __syncthreads();
+  env_sync<T, N>(ws);
   {
     uint32_t* d = (uint32_t*)&envs[env]; const uint32_t* s = (const uint32_t*)&ws.e;
     for (int i = tid; i < (int)(sizeof(EnvState<T, GMJ_WQC>) / 4); i += GMJ_WNT) d[i] = s[i];
@@ -277,11 +315,15 @@ k_step_wide(EnvState<T, GMJ_WQC>* __restrict__ envs, const DevModel<T, GMJ_WNT>*
 template <typename T, int N>
 int launch_step_wide_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
                         float* reward, uint8_t* done, float* events, cudaStream_t st) {
-  size_t smem = sizeof(WideShared<T, N>);
+  constexpr int EPB = WideCfg<T, N>::EPB;
+  const bool combined = (flags & STEP_COMBINED) != 0;
+  size_t smem = sizeof(WideShared<T, N>) * EPB;
   static bool attr_set = false;
   if (!attr_set) { CK(cudaFuncSetAttribute(k_step_wide<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
-  k_step_wide<T, N><<<h->n_envs, GMJ_WNT, smem, st>>>((EnvState<T, GMJ_WQC>*)h->envs, (const DevModel<T, GMJ_WNT>*)h->model, h->settings,
-      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag);
+  const int blocks = (h->n_envs + EPB - 1) / EPB;
+  const int list_blocks = combined ? blocks : 0;        // worst case every env owes a lift; empty list blocks exit at once
+  k_step_wide<T, N><<<blocks + list_blocks, GMJ_WNT * EPB, smem, st>>>((EnvState<T, GMJ_WQC>*)h->envs, (const DevModel<T, GMJ_WNT>*)h->model, h->settings,
+      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks, h->perm, h->hist);
   CK(cudaGetLastError());
   h->smem_bytes = smem;
   return 0;

@@ -43,8 +43,30 @@ struct WideShared : WarpShared<T, N, GMJ_WQC> {
   int cnt[2][4];                    // contacts per group: gripper-ground, gripper-object
   unsigned limmask[3];              // joint-limit violations per warp
   int ebad, extra;
+  int grp;                          // which env group of the block this is (named barrier 1 + grp)
   alignas(32) T colb[3][2][32];     // per-warp column broadcast of the factorisation (double buffered)
 };
+
+// Environments per block. FP32: as many as shared memory holds (4 at N = 24), run in LOCKSTEP like the lane-per-dof
+// kernel: the substep is ~12 k straight-line SASS instructions per warp, independent 96-thread blocks each streamed
+// their own copy (ncu r1: stall_no_inst 41 %); groups that share a block share the fetch stream. The three warps of
+// one env meet on named barrier 1 + grp (env_sync), the whole block on barrier 0 at the phase boundaries (wide_phase).
+template <typename T, int N> struct WideCfg {
+  static constexpr int FIT = (int)((227 * 1024 - 64) / sizeof(WideShared<T, N>));
+  static constexpr int EPB = sizeof(T) == 4 ? (FIT >= 4 ? 4 : (FIT >= 1 ? FIT : 1)) : 1;
+};
+#define GMJ_WNPHASE 6                // block-wide barriers inside one wide substep
+template <typename T, int N> __device__ __forceinline__ void env_sync(const WideShared<T, N>& ws) {
+  if (WideCfg<T, N>::EPB == 1) __syncthreads();
+  else asm volatile("bar.sync %0, %1;" :: "r"(ws.grp + 1), "n"(GMJ_WNT) : "memory");
+}
+template <typename T, int N> __device__ __forceinline__ void wide_phase() {
+  if (WideCfg<T, N>::EPB > 1) __syncthreads();
+}
+template <typename T, int N> __device__ __forceinline__ void wide_phase_idle() {
+#pragma unroll
+  for (int k = 0; k < GMJ_WNPHASE; k++) wide_phase<T, N>();
+}
 
 // sum K per-thread partials over the whole environment (3 warps); every thread gets the same totals
 template <typename T, int N, int K>
@@ -60,7 +82,7 @@ __device__ __forceinline__ void xsum(WideShared<T, N>& ws, int& xn, int w, int l
 #pragma unroll
     for (int m = 0; m < K; m++) buf[w][m] = v[m];
   }
-  __syncthreads();
+  env_sync<T, N>(ws);
 #pragma unroll
   for (int m = 0; m < K; m++) v[m] = buf[0][m] + buf[1][m] + buf[2][m];
   xn++;
@@ -181,7 +203,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
   const int lane = tp.lane, w = tp.w;
   EnvState<T, GMJ_WQC>& e = ws.e;
   int xn = 0;
-  if (e.unstable) { __syncthreads(); if (tid == 0) e.time += dtd; return; }
+  if (e.unstable) { wide_phase_idle<T, N>(); env_sync<T, N>(ws); if (tid == 0) e.time += dtd; return; }
   const T gz = -M.zref;
   T* L1w = &ws.L1[w][0][0];
   T* L2w = &ws.L2[w][0][0];
@@ -244,6 +266,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
   const T om = e.obj[9];
   const V3<T> oI = mk<T>(e.obj[10], e.obj[11], e.obj[12]);
 
+  wide_phase<T, N>();
   // ------------------------------------------------------------------ spatial quantities
   T mass = tp.act ? M.f[MF_mass][tid] : T(0);
   V3<T> c = p + mul(R, mk<T>(M.f[MF_ip0][tid], M.f[MF_ip1][tid], M.f[MF_ip2][tid]));
@@ -313,7 +336,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
       for (int k = 0; k < 6; k++) o[10 + k] = Ic.I[k];
     }
     if (tp.base) buf[w][16] = tb_tip;
-    __syncthreads();
+    env_sync<T, N>(ws);
     if (tp.base) {
 #pragma unroll 1
       for (int g = 0; g < 4; g++) {
@@ -364,6 +387,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
     for (int k = 0; k < 6; k++) rsqo[k] = T(1) / sqrtT<T>(Mo[k]);
   }
 
+  wide_phase<T, N>();
   // ------------------------------------------------------------------ factorisations
   T D, lb, D2, lb2;
   ldl_factor_w<T, N>(ws, xn, tp, Mrow, L1w, Mb, Mself, D, lb);
@@ -376,6 +400,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
   T wsm;
   { T x1[1] = { tp.act ? tau : T(0) }; fwd_w<T, N, 1, 0>(ws, xn, tp, L1w, lb, x1, nullptr); wsm = x1[0] * rsq; }
 
+  wide_phase<T, N>();
   // ------------------------------------------------------------------ collision
   Shape<T> so;
   so.type = (int)e.obj[0]; so.size = mk<T>(e.obj[1], e.obj[2], e.obj[3]); so.round = e.obj[4];
@@ -452,7 +477,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
     }
     if (lane == 31) { ws.cnt[0][w] = s2; ws.cnt[1][w] = s3; }
     if (tp.palm) { ws.cnt[0][3] = c2; ws.cnt[1][3] = c3; }
-    __syncthreads();
+    env_sync<T, N>(ws);
     const int grp = tp.palm ? 3 : w;
     int off2 = n1, off3 = n1 + ws.cnt[0][0] + ws.cnt[0][1] + ws.cnt[0][2] + ws.cnt[0][3];
     for (int g = 0; g < grp; g++) { off2 += ws.cnt[0][g]; off3 += ws.cnt[1][g]; }
@@ -485,9 +510,10 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
       if (hitg) { if (slot < GMJ_MAXCON) add_contact(pg + so.pos, ng, -depg, maxT<T>(gfric, ofric), tid, gcls, TW::OBJ, GMJ_CLS_OBJECT, slot); slot++; }
       if (hith) { if (slot < GMJ_MAXCON) add_contact(ph + so.pos, nh, -deph, maxT<T>(gfric, ofric), tid, gcls, TW::OBJ, GMJ_CLS_OBJECT, slot); slot++; }
     }
-    __syncthreads();
+    env_sync<T, N>(ws);
   }
 
+  wide_phase<T, N>();
   // ------------------------------------------------------------------ constraint rows
   int nr = 0;
   const T zero6[6] = { 0, 0, 0, 0, 0, 0 };
@@ -612,11 +638,12 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
     for (int k = 0; k < 6; k++) ws.W[nr][B + k] = tauo[k] * rsqo[k];
     ws.ax.ncon = ncon; ws.ax.nrow = nr;
   }
-  __syncthreads();
+  env_sync<T, N>(ws);
 
+  wide_phase<T, N>();
   // ------------------------------------------------------------------ A = W W^T, all 96 threads share the entries
   form_A<T, N, GMJ_WNT>(ws, nr, tid, nullptr);
-  __syncthreads();
+  env_sync<T, N>(ws);
   // ------------------------------------------------------------------ regulariser + dual LCP: warp 0
   int iters = 0;
   if (w == 0) {
@@ -665,8 +692,9 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
     if (r1 < nr) e.fprev[r1] = pf[1];
     if (lane == 0) { e.nrow_prev = nr; ws.ax.niter = iters; }
   }
-  __syncthreads();
+  env_sync<T, N>(ws);
 
+  wide_phase<T, N>();
   // ------------------------------------------------------------------ constraint force, integration
   T g = 0, go = 0;
   for (int r = 0; r < nr; r++) {
@@ -742,7 +770,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
   }
   unsigned anybad = __ballot_sync(GMJ_FULL, bad);
   if (anybad && lane == 0) ws.ebad = 1;
-  __syncthreads();
+  env_sync<T, N>(ws);
   if (tid == 0) {
     if (ws.ebad) e.unstable = 1;
     e.time += dtd;

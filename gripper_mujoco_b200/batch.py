@@ -100,10 +100,17 @@ class GripperBatch:
         m = self._mask(mask)
         check(self.L.gmj_spawn(self.h, _ptr(idx), _ptr(xyr), _ptr(m), 0.0, 0.0, self._stream()))
 
-    def spawn_into_scene(self, xy_range=0.0, rot_range=0.0, mask=None):
-        """Random object + pose per env from the device RNG (MjClass::spawn_into_scene)."""
+    def spawn_into_scene(self, xy_range=0.0, rot_range=0.0, mask=None, index=None):
+        """Random pose per env from the device RNG (MjClass::spawn_into_scene); the object too unless `index`
+        (scalar or per-env int array / tensor) names it, as spawn_into_scene(index) does."""
         m = self._mask(mask)
-        check(self.L.gmj_spawn(self.h, None, None, _ptr(m), float(xy_range), float(rot_range), self._stream()))
+        idx = None
+        if index is not None:
+            if torch.is_tensor(index):
+                idx = index.to(device=self.device, dtype=torch.int32).expand(self.n_envs).contiguous()
+            else:
+                idx = torch.as_tensor(np.broadcast_to(np.asarray(index, dtype=np.int32), (self.n_envs,)).copy(), device=self.device)
+        check(self.L.gmj_spawn(self.h, _ptr(idx), None, _ptr(m), float(xy_range), float(rot_range), self._stream()))
 
     def step(self, actions, frac=None):
         """Fused set_action -> action_step -> observation / reward / done / events (device tensors)."""

@@ -111,13 +111,15 @@ __global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const Dev
   const DevSettings& S = *Sp; const DevModelS<T>& M = *Mp;
   int oi; double x, y, rot;
   if (idx) {
-    oi = idx[env]; x = xyr[3 * env]; y = xyr[3 * env + 1]; rot = xyr[3 * env + 2];
+    oi = idx[env];
     if (oi < 0 || oi >= n_objects) { if (err_flag) atomicExch(err_flag, 2); return; }
-  } else {
-    // object index and pose from the counter-based RNG; candidate grid as in spawn_into_scene
-    // (2 mm steps within +-xy_range, pi/30 steps within +-rot_range), fingertip boxes from
-    // luke::get_finger_hook_locations (src/myfunctions.cpp:3717-3761), up to 16 candidates
-    oi = (int)(dev_uniform(e, S) * n_objects); if (oi >= n_objects) oi = n_objects - 1;
+  }
+  if (idx && xyr) { x = xyr[3 * env]; y = xyr[3 * env + 1]; rot = xyr[3 * env + 2]; }
+  else {
+    // object index (unless given: spawn_into_scene(index), src/mjclass.cpp:2422) and pose from the counter-based
+    // RNG; candidate grid as in spawn_into_scene (2 mm steps within +-xy_range, pi/30 steps within +-rot_range),
+    // fingertip boxes from luke::get_finger_hook_locations (src/myfunctions.cpp:3717-3761), up to 16 candidates
+    if (!idx) { oi = (int)(dev_uniform(e, S) * n_objects); if (oi >= n_objects) oi = n_objects - 1; }
     const GmjObject& ob = objects[oi];
     const double inc = 2e-3, rinc = 3.14159265358979323846 / 30.0, gap = 1e-3;
     int nx = (int)((2 * (double)xy_range) / inc) + 1, nrot = (int)((2 * (double)rot_range) / rinc) + 1;
@@ -481,7 +483,7 @@ int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const 
               float rot_range, void* stream) {
   if (!h) FAIL("null handle");
   if (!h->objects) FAIL("gmj_spawn before gmj_set_objects");
-  if (idx_dev && !xyr_dev) FAIL("gmj_spawn: idx_dev given without xyr_dev");
+  if (!idx_dev && xyr_dev) FAIL("gmj_spawn: xyr_dev given without idx_dev");
   CK(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;

@@ -278,7 +278,10 @@ template <typename T, int N, int QC>
 __device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b, const T* R, const int* type, T* f, bool warm) {
   constexpr int NW = WarpShared<T, N, QC>::NW;
   T* A = ws.A;
-  const T eps = sizeof(T) == 8 ? T(1e-12) : T(2e-6);
+#ifndef GMJ_LCP_EPS_WIDE
+#define GMJ_LCP_EPS_WIDE 2e-6
+#endif
+  const T eps = sizeof(T) == 8 ? T(1e-12) : (NW > 40 ? T(GMJ_LCP_EPS_WIDE) : T(2e-6));
   const int maxit = 40;
   const int r0 = lane, r1 = lane + 32;
   const bool two = nr > 32;

@@ -137,10 +137,17 @@ class MjClass:
             raise RuntimeError("bad index to spawn_object()")           # src/mjclass.cpp:2359-2362
         self.batch.spawn_object(index, x, y, zrot, mask)
 
-    def spawn_into_scene(self, xrange=None, rotrange=None, mask=None):
+    def spawn_into_scene(self, xrange=None, rotrange=None, mask=None, index=None):
+        """spawn_into_scene() / spawn_into_scene(index) (src/mjclass.cpp:2422-2654); always finds a pose here
+        (the device sampler falls back to its last candidate), so there is no `False` return to retry on."""
         d = self.default_spawn_params
+        if index is not None and not torch.is_tensor(index):
+            n = len(self._objects)
+            if np.any(np.asarray(index) < 0) or np.any(np.asarray(index) >= n):
+                raise RuntimeError("bad index to spawn_into_scene()")
         self.batch.spawn_into_scene(d.xrange if xrange is None else xrange,
-                                    d.rotrange if rotrange is None else rotrange, mask)
+                                    d.rotrange if rotrange is None else rotrange, mask, index)
+        return True
 
     def get_number_of_objects(self) -> int:
         return len(self._objects)

@@ -163,3 +163,14 @@ def pack_objects(specs) -> "ctypes array":
     for i, s in enumerate(specs):
         arr[i] = s.obj
     return arr
+
+
+def task_split(n_objects: int, seed: int = 102, obj_per_task: int = 20, shuffle: bool = True) -> list[np.ndarray]:
+    """`random_object_split` (description/mujoco/xml_script.py:603-660): shuffle every object of the set and cut
+    the order into task files of `obj_per_task`; MjEnv treats the first test_objects / test_obj_per_file files as
+    the test set and draws training tasks from the rest (rl/env/MjEnv.py:394-409). The permutation itself is not
+    pinned to the reference's (its generator runs after other draws in a separate process): restated, same law."""
+    order = np.arange(n_objects)
+    if shuffle:
+        np.random.RandomState(seed).shuffle(order)
+    return [order[i:i + obj_per_task] for i in range(0, n_objects, obj_per_task)]

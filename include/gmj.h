@@ -47,7 +47,8 @@ int gmj_reset(GmjHandle* h, const uint8_t* mask_dev, void* stream);
 /* idx_dev int32[n_envs], xyr_dev float[n_envs][3] (x, y, z-rotation); idx_dev == NULL draws object,
  * position (2 mm grid within +-xy_range) and rotation (pi/30 grid within +-rot_range) per env from the
  * counter-based RNG, rejecting poses that overlap the fingertip boxes (spawn_into_scene,
- * src/mjclass.cpp:2475-2654). mask_dev as above. */
+ * src/mjclass.cpp:2475-2654). idx_dev given with xyr_dev == NULL: that object at a random pose
+ * (spawn_into_scene(index), src/mjclass.cpp:2422-2473). mask_dev as above. */
 int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const uint8_t* mask_dev,
               float xy_range, float rot_range, void* stream);
 

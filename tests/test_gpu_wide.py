@@ -98,3 +98,20 @@ def test_wide_mjclass_autocalibration_n24():
     assert abs(mj.get_wrist_force()).max() < 5.0
     assert mj.batch.stats()["unstable_resets"] == 0
     mj.close()
+
+
+def test_wide_lockstep_blocks_with_mixed_lifts_fp32():
+    """FP32 packs four envs per lockstep block and schedules the envs that owe the termination lift (2S extra
+    substeps) into their own leading blocks: a ragged batch (10 envs = 2.5 blocks) where some envs terminate
+    on every step must still match the oracle env by env."""
+    n = 10
+    mdl, st = make_pair(16, DT[16], steps_per_action=40, noise=False)
+    gb, ob = _batch(n, mdl, st, "fp32"), OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    rng = np.random.default_rng(161)
+    term = gb.n_actions - 1
+    for t in range(6):
+        a = rng.integers(0, term, n).astype(np.int32)
+        a[rng.permutation(n)[: 1 + t % 3]] = term          # 1-3 lifting envs per step, different ones each time
+        _compare(gb, ob, a, "fp32")
+    gb.close()

@@ -177,6 +177,8 @@ __global__ void k_dump(const EnvState<T, QC>* envs, int n_envs, int B, double* q
     p[GP_cumulative_reward] = e.cumulative_reward; p[GP_has_object] = e.has_object; p[GP_obj_index] = e.obj_index;
     p[GP_episode] = e.episode; p[GP_last_reward] = e.last_reward; p[GP_last_done] = e.last_done;
     p[GP_nrow] = e.nrow_prev;
+    p[GP_niter] = e.st_substeps ? (double)e.st_iters / (double)e.st_substeps : 0.0;   // mean LCP pivoting rounds per substep so far
+    p[GP_ncon] = e.st_substeps ? (double)e.st_contacts / (double)e.st_substeps : 0.0;
   }
 }
 

@@ -25,9 +25,11 @@ g = torch.Generator(device="cpu"); g.manual_seed(0)
 acts = torch.randint(0, mj.get_n_actions() - 1, (steps, n), generator=g, dtype=torch.int32).to(mj.device)
 for k in range(steps):
     mj.fused_step(acts[k])
-    it = np.asarray(mj.batch.probe_field("niter")); nr = np.asarray(mj.batch.probe_field("nrow")); nc = np.asarray(mj.batch.probe_field("ncon"))
-    w = np.asarray(mj.batch.probe_field("weld_on")).astype(int)
-    print(f"step {k}: niter hist {np.bincount(it.astype(int), minlength=6)[:8]} max {it.max():.0f}  nrow mean {nr.mean():.1f}  "
-          f"niter>1: nrow {nr[it > 1].mean() if (it > 1).any() else 0:.1f} ncon {nc[it > 1].mean() if (it > 1).any() else 0:.1f} "
-          f"welds {np.bincount(w[it > 1], minlength=128).argmax() if (it > 1).any() else -1}; niter==1: nrow {nr[it == 1].mean():.1f} ncon {nc[it == 1].mean():.1f}")
+it = np.asarray(mj.batch.probe_field("niter")); nr = np.asarray(mj.batch.probe_field("nrow")); nc = np.asarray(mj.batch.probe_field("ncon"))
+print("mean rounds/substep per env: quantiles", np.quantile(it, [0, 0.5, 0.9, 0.99, 1.0]).round(2))
+order = np.argsort(-it)[:12]
+names = mj.get_current_object_name()
+for e in order:
+    print(f"  env {e:4d} rounds {it[e]:6.2f}  nrow(last) {nr[e]:3.0f}  mean contacts {nc[e]:5.2f}  {names[e]}")
+print("share of all rounds spent by the top 5 % envs:", np.sort(it)[-max(1, n // 20):].sum() / it.sum())
 print(mj.batch.stats())

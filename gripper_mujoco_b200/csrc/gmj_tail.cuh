@@ -442,7 +442,8 @@ __device__ inline int set_action(EnvState<T, QC>& e, const DevSettings& S, const
     if (kind == 0) wl = call_action(e, S, a, v);
     else if (kind == 1) wl = call_action(e, S, a, -1 * v);
     else {
-      if (fraction < -1.0f) fraction = -1.0f; else if (fraction > 1.0f) fraction = 1.0f;
+      // no clamp here: MjClass::set_action(int, float) takes the fraction as given, only
+      // set_continous_action clamps to [-1, 1] first (src/mjclass.cpp:1517-1526; host side: mjclass.py)
       wl = call_action(e, S, a, v * fraction);
       e.ev_value[GBE_COUNT + GLE_action_penalty_lin] += fabsf(fraction);
       e.ev_value[GBE_COUNT + GLE_action_penalty_sq] += fraction * fraction;

@@ -98,7 +98,9 @@ class MjClass:
     set_discrete_action = set_action
 
     def set_continous_action(self, action, fraction):
-        self.batch.set_action(action, fraction)
+        """src/mjclass.cpp:1517-1526: the magnitude fraction is clamped to [-1, 1] before set_action."""
+        f = torch.as_tensor(fraction, device=self.device, dtype=torch.float32).clamp(-1.0, 1.0)
+        self.batch.set_action(action, f)
 
     def action_step(self):
         self.batch.action_step()
@@ -119,7 +121,10 @@ class MjClass:
         return self.batch.observe(obs=False, reward=False, done=False, events=True)[3]
 
     def fused_step(self, actions, fractions=None):
-        """set_action + action_step + get_observation + reward + is_done in one launch."""
+        """set_action (set_continous_action when `fractions` is given: clamped to [-1, 1]) + action_step +
+        get_observation + reward + is_done in one launch."""
+        if fractions is not None:
+            fractions = torch.as_tensor(fractions, device=self.device, dtype=torch.float32).clamp(-1.0, 1.0)
         return self.batch.step(actions, fractions)
 
     def get_n_actions(self) -> int:

@@ -97,10 +97,10 @@ class OracleBatch:
                     float(np.broadcast_to(y, (len(self.envs),))[i]),
                     float(np.broadcast_to(r, (len(self.envs),))[i]))
 
-    def step(self, actions):
+    def step(self, actions, frac=None):
         obs, rew, done, ev = [], [], [], []
-        for e, a in zip(self.envs, actions):
-            rc = e.set_action(int(a))
+        for i, (e, a) in enumerate(zip(self.envs, actions)):
+            rc = e.set_action(int(a)) if frac is None else e.set_action(int(a), float(frac[i]))
             assert rc == 0
             e.action_step()
             obs.append(e.observation()); rew.append(e.reward()); done.append(e.is_done()); ev.append(e.event_state())

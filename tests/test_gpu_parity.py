@@ -354,3 +354,52 @@ def test_statistical_parity_random_grasps_fp32():
     freq_g, freq_o = e_g[:, :15].astype(bool).mean(axis=0), e_o[:, :15].astype(bool).mean(axis=0)
     assert np.abs(freq_g - freq_o).max() <= 0.03
     gb.close()
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_continuous_actions(precision):
+    """set_continous_action (src/mjclass.cpp:1517-1526, 1560-1630): one action per motor with a signed fraction of
+    its step (clamped to [-1, 1]), the termination action fires above termination_threshold only, the action
+    penalty events accumulate |f| and f^2. Fractions outside [-1, 1] and both sides of the threshold are drawn."""
+    n = 8
+    mdl, st = make_pair(5, 4e-3, noise=False)
+    st.continous_actions = True
+    gb, ob = _batch(n, mdl, st, precision), OracleBatch(n, mdl, st)
+    assert gb.n_actions == 8                      # 7 in-use actions + termination (header defaults)
+    gb.reset(); ob.reset()
+    idx = np.full(n, find_object("cube_fillet_0_3")[0], dtype=np.int32)
+    gb.spawn_object(idx, 0.0, 0.0, 0.0); ob.spawn(idx, 0.0, 0.0, 0.0)
+    rng = np.random.default_rng(21)
+    tq, tv, to, tr, te = TOL[precision]
+    for t in range(10):
+        a = rng.integers(0, gb.n_actions - 1, n).astype(np.int32)
+        f = rng.uniform(-1.3, 1.3, n).astype(np.float32)
+        if t >= 7:                                # termination with fractions around the threshold
+            a[: n // 2] = gb.n_actions - 1
+            f[: n // 2] = np.linspace(-0.5, 1.2, n // 2)
+        o_g, r_g, d_g, e_g = (v.cpu().numpy() for v in gb.step(a, f))
+        o_o, r_o, d_o, e_o = ob.step(a, f)
+        qg, _ = gb.state()
+        assert np.abs(qg - ob.qpos()).max() < tq and np.abs(o_g - o_o).max() < to and np.abs(r_g - r_o).max() < tr
+        assert np.array_equal(e_g[:, DISCRETE], e_o[:, DISCRETE]) and np.array_equal(d_g.astype(bool), d_o)
+        assert np.abs(e_g[:, CONTINUOUS] - e_o[:, CONTINUOUS]).max() < te
+    gb.close()
+
+
+def test_set_continous_action_clamps_on_the_host_side():
+    """MjClass.set_continous_action clamps the fraction like the reference's wrapper; gmj_set_action does not."""
+    from gripper_mujoco_b200.mjclass import MjClass
+    from gripper_mujoco_b200.model import GripperParams
+    from gripper_mujoco_b200.settings import Settings
+    st = Settings(); st.debug = False; st.set_use_noise(False); st.continous_actions = True
+    st.mujoco_timestep, st.sim_steps_per_action = 4e-3, 10
+    mj = MjClass(2, GripperParams(num_segments=5), settings=st, calibrate=False)
+    a = np.zeros(2, dtype=np.int32)
+    mj.set_continous_action(a, np.array([3.0, 1.0], dtype=np.float32))
+    x = mj.batch.probe_field("tend_x")
+    assert x[0] == x[1]                                   # 3.0 was clamped to 1.0
+    mj.reset()
+    mj.set_action(a, np.array([3.0, 1.0], dtype=np.float32))
+    x = mj.batch.probe_field("tend_x")
+    assert x[0] != x[1]                                   # raw set_action keeps the fraction
+    mj.close()

@@ -403,3 +403,35 @@ def test_set_continous_action_clamps_on_the_host_side():
     x = mj.batch.probe_field("tend_x")
     assert x[0] != x[1]                                   # raw set_action keeps the fraction
     mj.close()
+
+
+@pytest.mark.parametrize("mode", range(7))
+def test_observation_sampler_modes_and_sensor_sets(mode):
+    """get_observation (src/mjclass.cpp:1700-1959) under every sampler of MjType::Sensor (raw, change, average,
+    median, sign, scaled_change, scaled_change_sq; src/mjclass.h:278-453), history depths 1-3, and a sensor set that
+    differs from the header defaults (axial gauges and wrist XY on, palm off): same length and values as the oracle,
+    sign-mode entries exactly; rewards under a rescaled preset with a cap-style done trigger agree too."""
+    n = 4
+    mdl, st = make_pair(5, 4e-3, noise=True, seed=31 + mode)
+    st.sensor_sample_mode, st.state_sample_mode = mode, (mode + 3) % 7
+    st.sensor_n_prev_steps, st.state_n_prev_steps = 1 + mode % 3, 1 + (mode + 1) % 3
+    st.axial_gauge.in_use = True; st.wrist_sensor_XY.in_use = True; st.palm_sensor.in_use = (mode % 2 == 0)
+    st.scale_rewards(2.5)
+    st.object_contact.done, st.object_contact.trigger = 3, 1       # done once the contact event has fired 3 times
+    gb, ob = _batch(n, mdl, st, "fp32"), OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    idx = np.full(n, find_object("cube_fillet_0_3")[0], dtype=np.int32)
+    x = np.linspace(-0.006, 0.006, n).astype(np.float32)
+    gb.spawn_object(idx, x, 0.0, 0.2); ob.spawn(idx, x, 0.0, 0.2)
+    for t in range(10):
+        a = np.full(n, 1 if t < 8 else 5, dtype=np.int32)
+        o_g, r_g, d_g, e_g = (v.cpu().numpy() for v in gb.step(a))
+        o_o, r_o, d_o, e_o = ob.step(a)
+        assert o_g.shape == o_o.shape
+        assert np.abs(o_g - o_o).max() < 2e-2
+        if mode == 4:                                  # sign sampler: the derived entries are -1 / 0 / +1
+            sign_like = np.isin(o_o, (-1.0, 0.0, 1.0))
+            assert (np.abs(o_g - o_o)[sign_like] < 2e-2).all()
+        assert np.abs(r_g - r_o).max() < 2.5e-2
+        assert np.array_equal(d_g.astype(bool), d_o) and np.array_equal(e_g[:, DISCRETE], e_o[:, DISCRETE])
+    gb.close()

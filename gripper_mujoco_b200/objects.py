@@ -168,8 +168,10 @@ def pack_objects(specs) -> "ctypes array":
 def task_split(n_objects: int, seed: int = 102, obj_per_task: int = 20, shuffle: bool = True) -> list[np.ndarray]:
     """`random_object_split` (description/mujoco/xml_script.py:603-660): shuffle every object of the set and cut
     the order into task files of `obj_per_task`; MjEnv treats the first test_objects / test_obj_per_file files as
-    the test set and draws training tasks from the rest (rl/env/MjEnv.py:394-409). The permutation itself is not
-    pinned to the reference's (its generator runs after other draws in a separate process): restated, same law."""
+    the test set and draws training tasks from the rest (rl/env/MjEnv.py:394-409). xml_script.py seeds numpy with
+    the set's `fixed_random_seed` and draws nothing before the shuffle (:56-58, 645-647), so this is the same
+    permutation: the first 100 objects have exactly the category breakdown the reference documents for seed 102
+    (set9_fullset.yaml:47-55; tests/test_config.py)."""
     order = np.arange(n_objects)
     if shuffle:
         np.random.RandomState(seed).shuffle(order)

@@ -173,3 +173,39 @@ def test_oracle_rest_state_is_equilibrium():
     e.substep(200)
     assert np.abs(e.qpos()[:mdl.B] - q0[:mdl.B]).max() < 2e-5
     assert abs(e.peek().wrist_z + 2.375 * 9.81) < 0.05
+
+
+@pytest.mark.parametrize("N,dt", [(5, 4e-3), (8, 2e-3), (16, 8e-4)])
+def test_oracle_cantilever_matches_the_stiffness_derivation(N, dt):
+    """Analytic physics check. The reference's joint stiffnesses (src/myfunctions.cpp:988-1048:
+    c_1 = 2EI/L N^2/(N - 1/3), c_n = N EI/L) are derived so that N rigid links reproduce the Euler-Bernoulli tip
+    deflection F L^3 / 3EI of a tip load. The calibration load (apply_segment_force, :1642-1727) acts at the COM of
+    the last segment body, a < L, in the hook frame (15 degrees off the finger normal), so the static small-angle
+    answer of the discrete chain is  d = F_perp sum_i (a - x_i)(L - x_i) / c_i  with joints at x_i = (i-1) L/N.
+    The restated physics (oracle, soft welds, gravity on the hanging finger) settles within 3.5 % of it."""
+    from common import make_pair
+    from oracle.binding import OracleEnv
+    mdl, st = make_pair(N, dt, noise=False)
+    p = mdl.params
+    L, ell = p.finger_length, p.finger_length / N
+    seg = [b for b in mdl.bodies if b.name.startswith("finger_1_segment_link_")]
+    assert len(seg) == N
+    c = [b.stiffness for b in seg]
+    EI = p.finger_E * p.finger_width * p.finger_thickness ** 3 / 12
+    assert abs(c[1] / (N * EI / L) - 1) < 1e-6 and abs(c[0] / ((2 * EI / L) * N * N / (N - 1 / 3)) - 1) < 1e-6
+    x = np.arange(N) * ell
+    # with the load at the very tip the discrete chain gives Euler-Bernoulli exactly, for every N
+    assert abs(sum((L - x[i]) ** 2 / c[i] for i in range(N)) / (L ** 3 / (3 * EI)) - 1) < 1e-6
+    a = x[-1] + seg[-1].ipos[0]
+    F = 0.25
+    f_perp = F * np.cos(np.deg2rad(90.0 - p.hook_angle_degrees))
+    pred = f_perp * sum((a - x[i]) * (L - x[i]) / c[i] for i in range(N))
+    st.curve_validation, st.tip_force_applied = True, F
+    e = OracleEnv(mdl.to_struct(), st.pack())
+    e.reset(1, 0, 1)
+    e.substep(int(3.0 / dt))
+    q = e.qpos()
+    for f in range(3):
+        th = q[3 + f * (N + 2): 3 + f * (N + 2) + N]
+        d = float((ell * np.sin(np.cumsum(th))).sum())
+        assert abs(d / pred - 1) < 0.035, (f, d, pred)

@@ -435,3 +435,53 @@ def test_observation_sampler_modes_and_sensor_sets(mode):
         assert np.abs(r_g - r_o).max() < 2.5e-2
         assert np.array_equal(d_g.astype(bool), d_o) and np.array_equal(e_g[:, DISCRETE], e_o[:, DISCRETE])
     gb.close()
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+@pytest.mark.parametrize("thick,width", [(0.8e-3, 24e-3), (1.0e-3, 28e-3)])
+def test_finger_geometry_sweep_n8_grasp(precision, thick, width):
+    """The reference's trainings sweep finger thickness 0.8 / 0.9 / 1.0 mm and width 24 / 28 mm
+    (rl/TrainingManager.py, rl/env/MjEnv.py:338-392) at the default N = 8: the model builder follows (segment
+    inertia, stiffness EI N / L), and a grasp of three primitive classes matches the oracle on such a model too.
+    Also exercises settings away from the header defaults: no lift on termination, a tighter out-of-bounds radius."""
+    from gripper_mujoco_b200 import calibration
+    from gripper_mujoco_b200.model import GripperParams, build_model
+    from gripper_mujoco_b200.settings import Settings
+    from oracle.calibrate import make_backend
+    p = GripperParams(num_segments=8, finger_thickness=thick, finger_width=width)
+    mdl = build_model(p)
+    st = Settings()
+    st.mujoco_timestep, st.sim_steps_per_action = 2.5e-3, 40
+    calibration.calibrate_reset(p, mdl.N, mdl.B, st, make_backend(mdl))
+    st.set_use_noise(False); st.use_noise_seeded = 0; st.base_position_noise = 0.0
+    st.lift_on_termination = False
+    st.oob_distance = 0.02
+    n = 3
+    gb, ob = _batch(n, mdl, st, precision), OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    idx = np.array([find_object(nm)[0] for nm in OBJECTS[:3]], dtype=np.int32)
+    x = np.array([0.0, 0.018, -0.004], dtype=np.float32)          # the second object starts near the oob radius
+    gb.spawn_object(idx, x, 0.0, 0.1); ob.spawn(idx, x, 0.0, 0.1)
+    horizon = 12 if precision == "fp64" else 8
+    for t in range(horizon):
+        a = np.full(n, 1 if t < 7 else (5 if t < 10 else gb.n_actions - 1), dtype=np.int32)
+        _compare(gb, ob, a, precision)
+    s = gb.stats()
+    assert s["contacts"] > 0 and s["substeps"] == n * horizon * 40        # no 2S lift substeps were added
+    gb.close()
+
+
+def test_instability_is_flagged_like_the_oracle_fp64():
+    """is_sim_unstable / mj BADQACC stand-in (src/myfunctions.cpp:4233-4242): at a timestep far above the stable
+    range (SURVEY: 10.4 ms at N = 5) both sides freeze the env and count an unstable reset."""
+    mdl, st_bad = make_pair(5, 30e-3, steps_per_action=6, noise=False)
+    gb, ob = _batch(2, mdl, st_bad, "fp64"), OracleBatch(2, mdl, st_bad)
+    gb.reset(); ob.reset()
+    for t in range(6):
+        a = np.full(2, 1, dtype=np.int32)
+        gb.step(a); ob.step(a)
+    un_g = gb.probe_field("unstable").astype(bool)
+    un_o = np.array([bool(e.peek().unstable) for e in ob.envs])
+    assert un_g.all() and np.array_equal(un_g, un_o)
+    assert gb.stats()["unstable_resets"] == 2
+    gb.close()

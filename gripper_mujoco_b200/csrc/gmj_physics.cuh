@@ -28,6 +28,7 @@ struct WarpShared {
   T u[WS + 1];                      // W^T f scratch of the LCP solver
   T L2[3][N + 2][N + 3];            // second factor, for column access in the back substitution
   T qfk[QC];                        // qpos of the last kinematics pass (weld anchors)
+  T objv[32];                       // uniform over the lanes, kept out of registers: object smooth force, 1/sqrt(M), M (6 each), position (3), rotation (9)
   T rpos[GMJ_RMAX], rjv[GMJ_RMAX], rmu[GMJ_RMAX];
   int rtype[GMJ_RMAX], rfirst[GMJ_RMAX], rlane[GMJ_RMAX];
 };
@@ -454,15 +455,17 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
 #pragma unroll
     for (int k = 0; k < 9; k++) ws.ax.palmR[k] = R.m[k]; }
   // object (replicated in every lane)
-  V3<T> po = mk<T>(e.qpos[32], e.qpos[33], e.qpos[34] - M.zref);
-  M3<T> Ro;
-  { T a = e.qpos[35], b = e.qpos[36], c = e.qpos[37], d = e.qpos[38];
+  // object pose: one lane computes, everybody reads it back from shared memory where it is needed (objv)
+  T* const pov = ws.objv + 18; T* const Rov = ws.objv + 21;
+  if (lane == 0) {
+    pov[0] = e.qpos[32]; pov[1] = e.qpos[33]; pov[2] = e.qpos[34] - M.zref;
+    T a = e.qpos[35], b = e.qpos[36], c = e.qpos[37], d = e.qpos[38];
     T l = T(1) / sqrtT<T>(a * a + b * b + c * c + d * d);
-    Ro = quat2mat<T>(a * l, b * l, c * l, d * l); }
-  V3<T> vo = mk<T>(e.qvel[32], e.qvel[33], e.qvel[34]), wo = mk<T>(e.qvel[35], e.qvel[36], e.qvel[37]);
+    M3<T> Ro = quat2mat<T>(a * l, b * l, c * l, d * l);
+#pragma unroll
+    for (int k = 0; k < 9; k++) Rov[k] = Ro.m[k];
+  }
   const bool has_obj = e.has_object != 0;
-  const T om = e.obj[9];
-  const V3<T> oI = mk<T>(e.obj[10], e.obj[11], e.obj[12]);
 
   // ------------------------------------------------------------------ spatial quantities
   phase_barrier<NT>(1);
@@ -570,8 +573,12 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
     if (lane == 0) tau += tb;
   }
   // object smooth force (free joint: world linear dofs, body-frame angular dofs)
-  T tauo[6], rsqo[6], Mo[6];
-  {
+  // 18 values every lane would otherwise hold for the whole substep (ncu r1: spills were 20 % of the L1 traffic)
+  T* const tauo = ws.objv; T* const rsqo = ws.objv + 6; T* const Mo = ws.objv + 12;
+  if (lane == 0) {
+    const T om = e.obj[9];
+    const V3<T> oI = mk<T>(e.obj[10], e.obj[11], e.obj[12]);
+    const V3<T> wo = mk<T>(e.qvel[35], e.qvel[36], e.qvel[37]);
     V3<T> Iw = mk<T>(oI.x * wo.x, oI.y * wo.y, oI.z * wo.z);
     V3<T> gyr = cross(wo, Iw);
     tauo[0] = 0; tauo[1] = 0; tauo[2] = has_obj ? -om * M.gravity : T(0);
@@ -581,6 +588,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
 #pragma unroll
     for (int k = 0; k < 6; k++) rsqo[k] = T(1) / sqrtT<T>(Mo[k]);
   }
+  __syncwarp();
 
   // ------------------------------------------------------------------ factorisations
   phase_barrier<NT>(3);
@@ -606,7 +614,12 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   int ncon = 0;
   Shape<T> so;
   so.type = (int)e.obj[0]; so.size = mk<T>(e.obj[1], e.obj[2], e.obj[3]); so.round = e.obj[4];
-  so.pos = po; so.R = mul(Ro, quat2mat<T>(e.obj[5], e.obj[6], e.obj[7], e.obj[8]));
+  {
+    M3<T> Ro;
+#pragma unroll
+    for (int k = 0; k < 9; k++) Ro.m[k] = Rov[k];
+    so.pos = mk<T>(pov[0], pov[1], pov[2]); so.R = mul(Ro, quat2mat<T>(e.obj[5], e.obj[6], e.obj[7], e.obj[8]));
+  }
   const T ofric = e.obj[13];
   auto add_contact = [&](V3<T> pos, V3<T> n, T dist, T mu, int b1, int c1, int b2, int c2, int slot) {
     DevContact<T>& cn = ws.ax.con[slot];
@@ -794,10 +807,10 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
       for (int k = 0; k < 6; k++) Joc[ax3][k] = 0;
       if (b2 == B) {
         Joc[ax3][0] = d.x; Joc[ax3][1] = d.y; Joc[ax3][2] = d.z;
-        V3<T> r = cp - po;
+        V3<T> r = cp - mk<T>(pov[0], pov[1], pov[2]);
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-          V3<T> axk = mk<T>(Ro.m[k], Ro.m[3 + k], Ro.m[6 + k]);
+          V3<T> axk = mk<T>(Rov[k], Rov[3 + k], Rov[6 + k]);
           Joc[ax3][3 + k] = dot(d, cross(axk, r));
         }
       }
@@ -810,7 +823,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
     }
 #pragma unroll
     for (int ax3 = 0; ax3 < 3; ax3++)
-      jvc[ax3] += (b2 == B) ? (Joc[ax3][0] * vo.x + Joc[ax3][1] * vo.y + Joc[ax3][2] * vo.z + Joc[ax3][3] * wo.x + Joc[ax3][4] * wo.y + Joc[ax3][5] * wo.z) : T(0);
+      jvc[ax3] += (b2 == B) ? (Joc[ax3][0] * e.qvel[32] + Joc[ax3][1] * e.qvel[33] + Joc[ax3][2] * e.qvel[34] + Joc[ax3][3] * e.qvel[35] + Joc[ax3][4] * e.qvel[36] + Joc[ax3][5] * e.qvel[37]) : T(0);
     const bool gripper_part = (b1 >= 0 && b1 < B) || (b2 >= 0 && b2 < B);
     T xw[3] = { Jc[0], Jc[1], Jc[2] };
     if (gripper_part) ldl_fwdK<T, N, 3>(tp, Mrow, lb, xw);      // object-ground contacts have no gripper columns
@@ -927,6 +940,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
 #pragma unroll
     for (int k = 0; k < 6; k++) { T gk = __shfl_sync(GMJ_FULL, go, k); ao[k] = (tauo[k] + gk / rsqo[k]) / Mo[k]; bad |= !(absT<T>(ao[k]) < T(1e10)); }
     if (lane == 0) {
+      V3<T> vo = mk<T>(e.qvel[32], e.qvel[33], e.qvel[34]), wo = mk<T>(e.qvel[35], e.qvel[36], e.qvel[37]);
       vo = vo + mk<T>(ao[0], ao[1], ao[2]) * dt; wo = wo + mk<T>(ao[3], ao[4], ao[5]) * dt;
       e.qvel[32] = vo.x; e.qvel[33] = vo.y; e.qvel[34] = vo.z; e.qvel[35] = wo.x; e.qvel[36] = wo.y; e.qvel[37] = wo.z;
       e.qpos[32] += dt * vo.x; e.qpos[33] += dt * vo.y; e.qpos[34] += dt * vo.z;

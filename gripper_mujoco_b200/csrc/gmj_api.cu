@@ -155,7 +155,7 @@ __global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const Dev
   e.qpos[OQ + 3] = (T)sin(-rot / 2.0); e.qpos[OQ + 4] = 0; e.qpos[OQ + 5] = 0; e.qpos[OQ + 6] = (T)cos(-rot / 2.0);
   for (int k = 0; k < 6; k++) e.qvel[OQ + k] = 0;
   e.start_z = (double)(T)z;
-  e.nrow_prev = 0;
+  e.nrow_prev = 0; e.mpr_prev = 0;
 }
 
 template <typename T, int QC>

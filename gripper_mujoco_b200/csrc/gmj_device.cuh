@@ -50,6 +50,7 @@ struct EnvState {
   uint32_t rng_ctr, env_id, episode, obj_index;
   unsigned long long st_contacts, st_rows, st_iters, st_substeps;
   unsigned int st_unstable, st_overflow, pending_extra, sort_key;   // pending_extra: lift substeps owed by set_action
+  int mpr_prev;                     // MPR passes (0-2: finger plates, hooks) the last substep ran: load key of the lockstep sort
 };
 
 // model constants, lane-major [field][32] so a warp reads each field conflict-free

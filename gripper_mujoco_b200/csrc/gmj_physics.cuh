@@ -694,14 +694,16 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
     int hitg = 0, hith = 0; T depg = 0, deph = 0; V3<T> ng, nh, pg, ph;
     // queries run in coordinates relative to the object centre (keeps FP32 resolution)
     Shape<T> so0 = so; so0.pos = mk<T>(0, 0, 0);
+    bool rung = false, runh = false;
     if (gtype >= 0) {
       V3<T> d = sg.pos - so.pos; T rr = ro + shape_bound(sg);
-      if (dot(d, d) <= rr * rr) { Shape<T> s0 = sg; s0.pos = d; hitg = mpr_penetration<T>(s0, so0, &depg, &ng, &pg); }
+      if (dot(d, d) <= rr * rr) { Shape<T> s0 = sg; s0.pos = d; hitg = mpr_penetration<T>(s0, so0, &depg, &ng, &pg); rung = true; }
     }
     if (htype >= 0) {
       V3<T> d = sh.pos - so.pos; T rr = ro + shape_bound(sh);
-      if (dot(d, d) <= rr * rr) { Shape<T> s0 = sh; s0.pos = d; hith = mpr_penetration<T>(s0, so0, &deph, &nh, &ph); }
+      if (dot(d, d) <= rr * rr) { Shape<T> s0 = sh; s0.pos = d; hith = mpr_penetration<T>(s0, so0, &deph, &nh, &ph); runh = true; }
     }
+    { const int passes = (__any_sync(GMJ_FULL, rung) ? 1 : 0) + (__any_sync(GMJ_FULL, runh) ? 1 : 0); if (lane == 0) e.mpr_prev = passes; }
     unsigned mg = __ballot_sync(GMJ_FULL, hitg), mh = __ballot_sync(GMJ_FULL, hith);
     unsigned any = mg | mh;
     while (any) {
@@ -714,6 +716,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
       }
     }
   }
+  else if (lane == 0) e.mpr_prev = 0;
   __syncwarp();
 
   // ------------------------------------------------------------------ constraint rows

@@ -18,8 +18,21 @@
 #ifndef GMJ_LIFT_WPB
 #define GMJ_LIFT_WPB 12
 #endif
-#define GMJ_SORT_BUCKETS 16
+#ifndef GMJ_SORT_DIV
 #define GMJ_SORT_DIV 3
+#endif
+#define GMJ_SORT_ROWS ((GMJ_RMAX + GMJ_SORT_DIV) / GMJ_SORT_DIV)
+#define GMJ_SORT_BUCKETS (3 * GMJ_SORT_ROWS)
+// load key of an env: MPR passes of its last substep first (a pass costs the whole warp ~1.5 k instructions, whichever
+// lanes run it), constraint rows second -- the warps of a lockstep block then agree phase by phase, not only in total
+#ifndef GMJ_SORT_MPR
+#define GMJ_SORT_MPR 1
+#endif
+template <typename E> __device__ __forceinline__ int sort_key_of(const E& e) {
+  int rows = e.nrow_prev / GMJ_SORT_DIV; if (rows > GMJ_SORT_ROWS - 1) rows = GMJ_SORT_ROWS - 1;
+  int mpr = GMJ_SORT_MPR ? e.mpr_prev : 0; if (mpr < 0) mpr = 0; if (mpr > 2) mpr = 2;
+  return mpr * GMJ_SORT_ROWS + rows;
+}
 #ifndef GMJ_BLOCKS_PER_SM
 #define GMJ_BLOCKS_PER_SM 1
 #endif
@@ -133,7 +146,7 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
       e.pending_extra = extra;
       if (extra > 0) env_list[atomicAdd(env_count, 1)] = env;
       else {                               // load key: constraint rows of the last substep (contacts dominate the cost)
-        int key = e.nrow_prev / GMJ_SORT_DIV; if (key >= GMJ_SORT_BUCKETS) key = GMJ_SORT_BUCKETS - 1;
+        const int key = sort_key_of(e);
         e.sort_key = key; atomicAdd(&hist[key], 1);
       }
     }
@@ -262,7 +275,7 @@ k_step_wide(EnvState<T, GMJ_WQC>* __restrict__ envs, const DevModel<T, GMJ_WNT>*
       e.pending_extra = extra;
       if (extra > 0) env_list[atomicAdd(env_count, 1)] = env;
       else {
-        int key = e.nrow_prev / GMJ_SORT_DIV; if (key >= GMJ_SORT_BUCKETS) key = GMJ_SORT_BUCKETS - 1;
+        const int key = sort_key_of(e);
         e.sort_key = key; atomicAdd(&hist[key], 1);
       }
     }

@@ -44,6 +44,7 @@ struct WideShared : WarpShared<T, N, GMJ_WQC> {
   unsigned limmask[3];              // joint-limit violations per warp
   int ebad, extra;
   int grp;                          // which env group of the block this is (named barrier 1 + grp)
+  int mprw[3];                      // MPR passes per warp in the last collision phase
   alignas(32) T colb[3][2][32];     // per-warp column broadcast of the factorisation (double buffered)
 };
 
@@ -453,18 +454,21 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
     if (htype == GMJ_GEOM_BOX) { int n = plane_candidates<T>(sh, gz, pts, dd); for (int i = 0; i < n; i++) n2h += dd[i] < 0; }
     if (n2g > 4) n2g = 4; if (n2h > 4) n2h = 4;
   }
+  bool rung = false, runh = false;
   if (has_obj) {
     T ro = shape_bound(so);
     Shape<T> so0 = so; so0.pos = mk<T>(0, 0, 0);
     if (gtype >= 0) {
       V3<T> d = sg.pos - so.pos; T rr = ro + shape_bound(sg);
-      if (dot(d, d) <= rr * rr) { Shape<T> s0 = sg; s0.pos = d; hitg = mpr_penetration<T>(s0, so0, &depg, &ng, &pg); }
+      if (dot(d, d) <= rr * rr) { Shape<T> s0 = sg; s0.pos = d; hitg = mpr_penetration<T>(s0, so0, &depg, &ng, &pg); rung = true; }
     }
     if (htype >= 0) {
       V3<T> d = sh.pos - so.pos; T rr = ro + shape_bound(sh);
-      if (dot(d, d) <= rr * rr) { Shape<T> s0 = sh; s0.pos = d; hith = mpr_penetration<T>(s0, so0, &deph, &nh, &ph); }
+      if (dot(d, d) <= rr * rr) { Shape<T> s0 = sh; s0.pos = d; hith = mpr_penetration<T>(s0, so0, &deph, &nh, &ph); runh = true; }
     }
   }
+  // MPR passes this warp ran (load key of the lockstep sort, see sort_key_of): the env's figure is the max over its warps
+  { const int passes = (__any_sync(GMJ_FULL, rung) ? 1 : 0) + (__any_sync(GMJ_FULL, runh) ? 1 : 0); if (lane == 31) ws.mprw[w] = passes; }
   // slots in body order: chain of finger 0, 1, 2, then the palm; category (2) before category (3)
   int ncon;
   {
@@ -478,6 +482,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
     if (lane == 31) { ws.cnt[0][w] = s2; ws.cnt[1][w] = s3; }
     if (tp.palm) { ws.cnt[0][3] = c2; ws.cnt[1][3] = c3; }
     env_sync<T, N>(ws);
+    if (tid == 0) { int m = ws.mprw[0]; if (ws.mprw[1] > m) m = ws.mprw[1]; if (ws.mprw[2] > m) m = ws.mprw[2]; e.mpr_prev = m; }
     const int grp = tp.palm ? 3 : w;
     int off2 = n1, off3 = n1 + ws.cnt[0][0] + ws.cnt[0][1] + ws.cnt[0][2] + ws.cnt[0][3];
     for (int g = 0; g < grp; g++) { off2 += ws.cnt[0][g]; off3 += ws.cnt[1][g]; }

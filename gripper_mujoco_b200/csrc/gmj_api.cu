@@ -429,6 +429,7 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
     // B200 (profiles/README.md): no gain on the bench workload, 7 % slower on the lift-free profile workload -> off.
     const char* bal = getenv("GMJ_BALANCE");
     h->balance_sm = (bal && atoi(bal) == 1) ? nsm : 0;
+    h->n_sm = nsm;
   }
   int rc;
   if (!h->wide) rc = precision == 0 ? upload_model<float, 32>(h, model) : upload_model<double, 32>(h, model);

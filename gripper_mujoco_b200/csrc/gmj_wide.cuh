@@ -736,7 +736,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
   // Euler with implicit damping: (M + h D) a = tau + tau_c
   T x;
   { T x1[1] = { tp.act ? tau + tauc : T(0) }; fwd_w<T, N, 1, 0>(ws, xn, tp, L2w, lb2, x1, nullptr); x = x1[0]; }
-  x = tp.act ? x / D2 : T(0);
+  x = tp.act ? x / (tp.act ? D2 : T(1)) : T(0);
   {
     T xb = __shfl_sync(GMJ_FULL, x, TW::BASE_L);
     if (tp.chain || tp.palm) x -= lb2 * xb;

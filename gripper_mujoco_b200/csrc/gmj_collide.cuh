@@ -9,6 +9,9 @@
 template <typename T>
 struct Shape { int type; V3<T> size; T round; V3<T> pos; M3<T> R; };
 
+#ifndef GMJ_CINL
+#define GMJ_CINL inline
+#endif
 template <typename T> __device__ __forceinline__ T shape_bound(const Shape<T>& s) {
   T r;
   if (s.type == GMJ_GEOM_BOX) r = sqrtT<T>(dot(s.size, s.size));
@@ -68,7 +71,7 @@ template <typename T> __device__ inline void tri_closest_origin(V3<T> a, V3<T> b
 
 // 1 on penetration; normal points from A to B, depth > 0, pos = contact point
 template <typename T>
-__device__ inline int mpr_penetration(const Shape<T>& A, const Shape<T>& B, T* depth, V3<T>* normal, V3<T>* pos) {
+__device__ GMJ_CINL int mpr_penetration(const Shape<T>& A, const Shape<T>& B, T* depth, V3<T>* normal, V3<T>* pos) {
   MV<T> v0, v1, v2, v3, v4;
   V3<T> n;
   v0.v = A.pos - B.pos; v0.a = A.pos; v0.b = B.pos;
@@ -140,7 +143,7 @@ template <typename T> __device__ inline void make_frame(V3<T> n, T* f) {
 // candidate plane points of one shape against the ground plane z = gz (normal +z). Returns count;
 // pts[i] = point on the swept surface, d[i] = signed distance.
 template <typename T>
-__device__ inline int plane_candidates(const Shape<T>& s, T gz, V3<T>* pts, T* d) {
+__device__ GMJ_CINL int plane_candidates(const Shape<T>& s, T gz, V3<T>* pts, T* d) {
   int n = 0;
   if (s.pos.z - gz - shape_bound(s) > 0) return 0;
   if (s.type == GMJ_GEOM_ELLIPSOID) {

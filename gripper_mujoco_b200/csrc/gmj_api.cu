@@ -5,17 +5,23 @@
 static thread_local std::string g_err;
 void gmj_set_error(const std::string& msg) { g_err = msg; }
 
-// counting-sort scatter of the envs that owe no lift substeps: perm[offset(key) + slot] = env
+// counting-sort scatter by load key, heaviest first: envs that owe no lift substeps into perm, the lifting envs
+// into env_list. hist = [counts | cursors | lifter counts | lifter cursors], GMJ_SORT_BUCKETS each.
 template <typename T, int QC>
-__global__ void k_sort_scatter(const EnvState<T, QC>* __restrict__ envs, int n_envs, const int* __restrict__ hist,
-                               int* __restrict__ cursor, int* __restrict__ perm) {
+__global__ void k_sort_scatter(const EnvState<T, QC>* __restrict__ envs, int n_envs, int* __restrict__ hist,
+                               int* __restrict__ perm, int* __restrict__ env_list, int sort_lift) {
   int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= n_envs) return;
-  if (envs[env].pending_extra > 0) return;
-  const int key = (int)envs[env].sort_key;
+  const bool lift = envs[env].pending_extra > 0;
+  const int* cnt = hist + (lift ? 2 * GMJ_SORT_BUCKETS : 0);
+  int* cursor = hist + (lift ? 3 * GMJ_SORT_BUCKETS : GMJ_SORT_BUCKETS);
+  // small launches keep the lifting envs in arrival order: the step is as long as the slowest lift block, and a block
+  // of equally heavy envs is slower than one heavy env among light ones (measured: +5 % step time at 4096 envs sorted,
+  // -3.5 % at 16384)
+  const int key = (lift && !sort_lift) ? GMJ_SORT_BUCKETS - 1 : (int)envs[env].sort_key;
   int off = 0;
-  for (int k = GMJ_SORT_BUCKETS - 1; k > key; k--) off += hist[k];      // heaviest first
-  perm[off + atomicAdd(&cursor[key], 1)] = env;
+  for (int k = GMJ_SORT_BUCKETS - 1; k > key; k--) off += cnt[k];
+  (lift ? env_list : perm)[off + atomicAdd(&cursor[key], 1)] = env;
 }
 
 // MjClass::reset + luke::reset (src/mjclass.cpp:434-486, src/myfunctions.cpp:544-570): one thread per env
@@ -448,7 +454,7 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
   CK(cudaMalloc(&h->stats_dev, 8 * sizeof(unsigned long long)));
   CK(cudaMalloc(&h->env_list, sizeof(int) * (size_t)n_envs)); CK(cudaMalloc(&h->env_count, sizeof(int)));
   CK(cudaMemset(h->env_count, 0, sizeof(int)));
-  CK(cudaMalloc(&h->perm, sizeof(int) * (size_t)n_envs)); CK(cudaMalloc(&h->hist, sizeof(int) * 2 * GMJ_SORT_BUCKETS));
+  CK(cudaMalloc(&h->perm, sizeof(int) * (size_t)n_envs)); CK(cudaMalloc(&h->hist, sizeof(int) * 4 * GMJ_SORT_BUCKETS));
   if (gmj_set_settings(h, settings)) { return 1; }
   *out = h;
   return gmj_reset(h, nullptr, nullptr);
@@ -503,10 +509,11 @@ int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const 
 static int launch_collect(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, void* stream) {
   CK(cudaSetDevice(h->device));
   CK(cudaMemsetAsync(h->env_count, 0, sizeof(int), (cudaStream_t)stream));
-  CK(cudaMemsetAsync(h->hist, 0, sizeof(int) * 2 * GMJ_SORT_BUCKETS, (cudaStream_t)stream));
+  CK(cudaMemsetAsync(h->hist, 0, sizeof(int) * 4 * GMJ_SORT_BUCKETS, (cudaStream_t)stream));
   if (launch_step(h, STEP_SET_ACTION | STEP_COLLECT, 0, actions_dev, frac_dev, nullptr, nullptr, nullptr, nullptr, stream)) return 1;
   int tb = 256, nb = (h->n_envs + tb - 1) / tb;
-  GMJ_FOR_STATE(h, k_sort_scatter<T, QC><<<nb, tb, 0, (cudaStream_t)stream>>>((const EnvState<T, QC>*)h->envs, h->n_envs, h->hist, h->hist + GMJ_SORT_BUCKETS, h->perm));
+  const int sort_lift = h->n_sm > 0 && h->n_envs > 3 * h->n_sm * 12;
+  GMJ_FOR_STATE(h, k_sort_scatter<T, QC><<<nb, tb, 0, (cudaStream_t)stream>>>((const EnvState<T, QC>*)h->envs, h->n_envs, h->hist, h->perm, h->env_list, sort_lift));
   CK(cudaGetLastError());
   return 0;
 }

@@ -145,11 +145,10 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
     }
     if ((flags & STEP_COLLECT) && lane == 0) {
       e.pending_extra = extra;
-      if (extra > 0) env_list[atomicAdd(env_count, 1)] = env;
-      else {                               // load key: constraint rows of the last substep (contacts dominate the cost)
-        const int key = sort_key_of(e);
-        e.sort_key = key; atomicAdd(&hist[key], 1);
-      }
+      const int key = sort_key_of(e);      // load key of the lockstep sort (k_sort_scatter fills perm / env_list)
+      e.sort_key = key;
+      if (extra > 0) { atomicAdd(env_count, 1); atomicAdd(&hist[2 * GMJ_SORT_BUCKETS + key], 1); }
+      else atomicAdd(&hist[key], 1);
     }
     extra = __shfl_sync(GMJ_FULL, extra, 0);
     __syncwarp();
@@ -277,11 +276,10 @@ k_step_wide(EnvState<T, GMJ_WQC>* __restrict__ envs, const DevModel<T, GMJ_WNT>*
     ws.extra = extra;
     if (flags & STEP_COLLECT) {
       e.pending_extra = extra;
-      if (extra > 0) env_list[atomicAdd(env_count, 1)] = env;
-      else {
-        const int key = sort_key_of(e);
-        e.sort_key = key; atomicAdd(&hist[key], 1);
-      }
+      const int key = sort_key_of(e);
+      e.sort_key = key;
+      if (extra > 0) { atomicAdd(env_count, 1); atomicAdd(&hist[2 * GMJ_SORT_BUCKETS + key], 1); }
+      else atomicAdd(&hist[key], 1);
     }
   }
   if (list_block && valid && tid == 0) { ws.extra = (int)e.pending_extra; e.pending_extra = 0; }

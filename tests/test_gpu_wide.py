@@ -139,3 +139,36 @@ def test_wide_lcp_rounds_with_long_objects(precision):
     assert s1["contacts"] > s0["contacts"]
     assert rounds < 1.25, f"{rounds:.2f} pivoting rounds per substep"
     gb.close()
+
+
+def test_wide_statistical_parity_random_grasps_n24_fp32():
+    """The contact-rich protocol of test_statistical_parity_random_grasps_fp32 on the wide kernel: 24 envs with random
+    objects of the full set (long bars and lying cylinders included) and poses under N = 24 fingers, 8 random actions
+    biased towards closing and lowering, FP32 CUDA vs the FP64 oracle env by env."""
+    n, steps = 24, 8
+    mdl, st = make_pair(24, DT[24], steps_per_action=60, noise=False)
+    gb, ob = _batch(n, mdl, st, "fp32"), OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    rng = np.random.default_rng(24)
+    idx = rng.integers(0, len(objects()), n).astype(np.int32)
+    x = (rng.integers(-5, 6, n) * 2e-3).astype(np.float32); y = (rng.integers(-5, 6, n) * 2e-3).astype(np.float32)
+    r = (rng.integers(-15, 16, n) * (np.pi / 30)).astype(np.float32)
+    gb.spawn_object(idx, x, y, r); ob.spawn(idx, x, y, r)
+    s0 = gb.stats()
+    rows, dones = [], []
+    for t in range(steps):
+        a = rng.integers(0, gb.n_actions - 1, n).astype(np.int32)
+        bias = rng.random(n) < 0.5
+        a[bias] = rng.choice([1, 3, 5, 13], size=int(bias.sum()))
+        o_g, r_g, d_g, e_g = (v.cpu().numpy() for v in gb.step(a))
+        o_o, r_o, d_o, e_o = ob.step(a)
+        rows.append((e_g[:, DISCRETE] == e_o[:, DISCRETE]).all(axis=1).mean())
+        dones.append((d_g.astype(bool) == d_o).mean())
+        assert np.abs(r_g - r_o).mean() < 5e-3
+    s1 = gb.stats()
+    dq = np.abs(gb.state()[0] - ob.qpos()).max(axis=1)
+    assert s1["contacts"] > s0["contacts"]
+    assert (s1["solver_iters"] - s0["solver_iters"]) / (s1["substeps"] - s0["substeps"]) < 1.1
+    assert min(rows) >= 0.85 and min(dones) >= 0.95, (rows, dones)
+    assert np.median(dq) < 1e-4
+    gb.close()

@@ -279,8 +279,10 @@ __device__ void form_A(WarpShared<T, N, QC>& ws, int nr, int lane, T* bcol) {   
 // reached) and gets w on the inactive rows from W (w = W (W^T f) + b). A second round has to rebuild
 // A from W first; with the warm-started active set that happens in about 1 % of the substeps.
 // Lane owns rows lane and lane + 32; b, R, type, f are per owned row. Returns the number of rounds.
-template <typename T, int N, int QC>
-__device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b, const T* R, const int* type, T* f, bool warm) {
+// TWO = false: nr <= 32, one row slot per lane -- the usual case (17 rows on average), compiled without the
+// second-slot arithmetic and the slot selects
+template <typename T, int N, int QC, bool TWO>
+__device__ int lcp_solve_impl(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b, const T* R, const int* type, T* f, bool warm) {
   constexpr int NW = WarpShared<T, N, QC>::NW;
   T* A = ws.A;
 #ifndef GMJ_LCP_GROW
@@ -293,11 +295,11 @@ __device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b,
   const T eps = sizeof(T) == 8 ? T(1e-12) : (NW > 40 ? T(GMJ_LCP_EPS_WIDE) : T(2e-6));
   const int maxit = 40;
   const int r0 = lane, r1 = lane + 32;
-  const bool two = nr > 32;
+  const bool two = TWO && nr > 32;
   bool act0, act1;
   act0 = r0 < nr && (type[0] == ROW_EQ || (warm ? f[0] > 0 : b[0] < 0));
-  act1 = r1 < nr && (type[1] == ROW_EQ || (warm ? f[1] > 0 : b[1] < 0));
-  T bscale = warp_max(maxT<T>(r0 < nr ? absT<T>(b[0]) : T(0), r1 < nr ? absT<T>(b[1]) : T(0)));
+  act1 = (TWO && r1 < nr) && (type[1] == ROW_EQ || (warm ? f[1] > 0 : b[1] < 0));
+  T bscale = warp_max(maxT<T>(r0 < nr ? absT<T>(b[0]) : T(0), (TWO && r1 < nr) ? absT<T>(b[1]) : T(0)));
   int best = 1 << 30, patience = 3, it = 0;
   T x0 = 0, x1 = 0;
   for (;; ) {
@@ -310,14 +312,15 @@ __device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b,
     T ld0 = 1, ld1 = 1;                       // 1 / L[r][r] of the owned rows
     const int t0 = TRI(r0, 0), t1 = TRI(r1, 0);
     for (int j = 0; j < nr; j++) {
-      const bool jact = j < 32 ? ((m0 >> j) & 1) : ((m1 >> (j - 32)) & 1);
+      const bool jact = (!TWO || j < 32) ? ((m0 >> j) & 1) : ((m1 >> (j - 32)) & 1);
       const int tj = TRI(j, 0);
-      const T Rj = __shfl_sync(GMJ_FULL, j < 32 ? R[0] : R[1], j & 31);
+      const T Rj = __shfl_sync(GMJ_FULL, (!TWO || j < 32) ? R[0] : R[1], j & 31);
       T inv = 1;
 #pragma unroll 1
       for (int base = j; base < nr; base += 32) {
+        if (!TWO && base != j) break;
         const int i = base + lane;
-        const bool iact = i < nr && ((i < 32 ? (m0 >> i) : (m1 >> (i - 32))) & 1);
+        const bool iact = i < nr && (((!TWO || i < 32) ? (m0 >> i) : (m1 >> (i - 32))) & 1);
         const int ti = TRI(i, 0);
         T sv = 0;
         if (jact && iact) {
@@ -340,15 +343,15 @@ __device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b,
     // ---- forward substitution L y = -b_F
     T y0 = act0 ? -b[0] : T(0), y1 = act1 ? -b[1] : T(0);
     for (int j = 0; j < nr; j++) {
-      T yj = __shfl_sync(GMJ_FULL, j < 32 ? y0 * ld0 : y1 * ld1, j & 31);
+      T yj = __shfl_sync(GMJ_FULL, (!TWO || j < 32) ? y0 * ld0 : y1 * ld1, j & 31);
       if (r0 == j) y0 = yj;
       if (r1 == j) y1 = yj;
       if (r0 > j && r0 < nr) y0 -= A[t0 + j] * yj;
-      if (two && r1 > j && r1 < nr) y1 -= A[t1 + j] * yj;
+      if (two && r1 > j && (TWO && r1 < nr)) y1 -= A[t1 + j] * yj;
     }
     // ---- back substitution L^T x = y
     for (int j = nr - 1; j >= 0; j--) {
-      T xj = __shfl_sync(GMJ_FULL, j < 32 ? y0 * ld0 : y1 * ld1, j & 31);
+      T xj = __shfl_sync(GMJ_FULL, (!TWO || j < 32) ? y0 * ld0 : y1 * ld1, j & 31);
       if (r0 == j) y0 = xj;
       if (r1 == j) y1 = xj;
       const int tj = TRI(j, 0);
@@ -363,7 +366,7 @@ __device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b,
 #pragma unroll
       for (int s = 0; s < NS; s++) u[s] = 0;
       for (int c = 0; c < nr; c++) {
-        T xc = __shfl_sync(GMJ_FULL, c < 32 ? x0 : x1, c & 31);
+        T xc = __shfl_sync(GMJ_FULL, (!TWO || c < 32) ? x0 : x1, c & 31);
 #pragma unroll
         for (int s = 0; s < NS; s++) if (lane + 32 * s < NW) u[s] += ws.W[c][lane + 32 * s] * xc;
       }
@@ -371,9 +374,9 @@ __device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b,
       for (int s = 0; s < NS; s++) if (lane + 32 * s < NW) ws.u[lane + 32 * s] = u[s];
       __syncwarp();
     }
-    T w0 = r0 < nr ? b[0] : T(0), w1 = r1 < nr ? b[1] : T(0);
+    T w0 = r0 < nr ? b[0] : T(0), w1 = (TWO && r1 < nr) ? b[1] : T(0);
     if (r0 < nr && !act0) { T a = 0; for (int k = 0; k < NW; k++) a += ws.W[r0][k] * ws.u[k]; w0 += a; }
-    if (two && r1 < nr && !act1) { T a = 0; for (int k = 0; k < NW; k++) a += ws.W[r1][k] * ws.u[k]; w1 += a; }
+    if (two && (TWO && r1 < nr) && !act1) { T a = 0; for (int k = 0; k < NW; k++) a += ws.W[r1][k] * ws.u[k]; w1 += a; }
     T fscale = warp_max(maxT<T>(absT<T>(x0), absT<T>(x1)));
     // Safety net against pivoting on rounding noise: the tolerance widens x16 per round from the third round on
     // (capped at 1e-2). Systems that converge in one or two rounds -- 99 % of the substeps at every N -- never see
@@ -382,7 +385,7 @@ __device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b,
     for (int k = GMJ_LCP_GROW_FROM; k < it && epsr < T(1e-2); k++) epsr *= GMJ_LCP_GROW;
     const T tolf = epsr * (1 + fscale), tolw = epsr * (1 + bscale);
     bool bad0 = r0 < nr && type[0] != ROW_EQ && (act0 ? x0 < -tolf : w0 < -tolw);
-    bool bad1 = r1 < nr && type[1] != ROW_EQ && (act1 ? x1 < -tolf : w1 < -tolw);
+    bool bad1 = (TWO && r1 < nr) && type[1] != ROW_EQ && (act1 ? x1 < -tolf : w1 < -tolw);
     const unsigned b0 = __ballot_sync(GMJ_FULL, bad0), b1 = __ballot_sync(GMJ_FULL, bad1);
     const int ninf = __popc(b0) + __popc(b1);
     if (ninf == 0 || it >= maxit) break;
@@ -400,6 +403,12 @@ __device__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b,
   f[0] = (type[0] != ROW_EQ && x0 < 0) ? T(0) : x0;
   f[1] = (type[1] != ROW_EQ && x1 < 0) ? T(0) : x1;
   return it;
+}
+
+template <typename T, int N, int QC>
+__device__ __forceinline__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int lane, const T* b, const T* R, const int* type, T* f, bool warm) {
+  return nr > 32 ? lcp_solve_impl<T, N, QC, true>(ws, nr, lane, b, R, type, f, warm)
+                 : lcp_solve_impl<T, N, QC, false>(ws, nr, lane, b, R, type, f, warm);
 }
 
 // ------------------------------------------------------------------ block lockstep

@@ -337,7 +337,7 @@ __device__ int lcp_solve_impl(WarpShared<T, N, QC>& ws, int nr, int lane, const 
         if (i > j && i < nr) A[ti + j] = sv * inv;
       }
       if (r0 == j) ld0 = inv;
-      if (r1 == j) ld1 = inv;
+      if (TWO && r1 == j) ld1 = inv;
       __syncwarp();
     }
     // ---- forward substitution L y = -b_F
@@ -345,7 +345,7 @@ __device__ int lcp_solve_impl(WarpShared<T, N, QC>& ws, int nr, int lane, const 
     for (int j = 0; j < nr; j++) {
       T yj = __shfl_sync(GMJ_FULL, (!TWO || j < 32) ? y0 * ld0 : y1 * ld1, j & 31);
       if (r0 == j) y0 = yj;
-      if (r1 == j) y1 = yj;
+      if (TWO && r1 == j) y1 = yj;
       if (r0 > j && r0 < nr) y0 -= A[t0 + j] * yj;
       if (two && r1 > j && (TWO && r1 < nr)) y1 -= A[t1 + j] * yj;
     }
@@ -353,14 +353,15 @@ __device__ int lcp_solve_impl(WarpShared<T, N, QC>& ws, int nr, int lane, const 
     for (int j = nr - 1; j >= 0; j--) {
       T xj = __shfl_sync(GMJ_FULL, (!TWO || j < 32) ? y0 * ld0 : y1 * ld1, j & 31);
       if (r0 == j) y0 = xj;
-      if (r1 == j) y1 = xj;
+      if (TWO && r1 == j) y1 = xj;
       const int tj = TRI(j, 0);
       if (r0 < j) y0 -= A[tj + r0] * xj;
       if (two && r1 < j) y1 -= A[tj + r1] * xj;
     }
     x0 = act0 ? y0 : T(0); x1 = act1 ? y1 : T(0);
-    // ---- w = W (W^T x) + b on the inactive rows
-    {
+    // ---- w = W (W^T x) + b on the inactive rows (skipped when every row is active: nothing to check there)
+    const bool need_w = __any_sync(GMJ_FULL, (r0 < nr && !act0) || (TWO && r1 < nr && !act1));
+    if (need_w) {
       constexpr int NS = (NW + 31) / 32;       // column slots per lane: lane, lane + 32, ... (NW = 86 at N = 24)
       T u[NS];
 #pragma unroll
@@ -397,7 +398,7 @@ __device__ int lcp_solve_impl(WarpShared<T, N, QC>& ws, int nr, int lane, const 
     else {                                     // Murty: flip only the infeasible row of largest index
       int top = b1 ? 32 + (31 - __clz(b1)) : (31 - __clz(b0));
       if (r0 == top) act0 = !act0;
-      if (r1 == top) act1 = !act1;
+      if (TWO && r1 == top) act1 = !act1;
     }
   }
   f[0] = (type[0] != ROW_EQ && x0 < 0) ? T(0) : x0;

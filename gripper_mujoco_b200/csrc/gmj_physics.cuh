@@ -324,11 +324,15 @@ __device__ int lcp_solve_impl(WarpShared<T, N, QC>& ws, int nr, int lane, const 
         const int ti = TRI(i, 0);
         T sv = 0;
         if (jact && iact) {
-          T a = A[ti + j], c = 0;
+          T a = A[ti + j], c = 0, a2 = 0, c2 = 0;       // four chains: the loads, not the FMAs, bound this loop
           int k = 0;
+          for (; k + 3 < j; k += 4) {
+            a -= A[ti + k] * A[tj + k]; c -= A[ti + k + 1] * A[tj + k + 1];
+            a2 -= A[ti + k + 2] * A[tj + k + 2]; c2 -= A[ti + k + 3] * A[tj + k + 3];
+          }
           for (; k + 1 < j; k += 2) { a -= A[ti + k] * A[tj + k]; c -= A[ti + k + 1] * A[tj + k + 1]; }
           if (k < j) a -= A[ti + k] * A[tj + k];
-          sv = a + c + (i == j ? Rj : T(0));
+          sv = (a + a2) + (c + c2) + (i == j ? Rj : T(0));
         }
         if (base == j) {
           const T dj = __shfl_sync(GMJ_FULL, sv, 0);

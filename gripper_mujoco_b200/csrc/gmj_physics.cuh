@@ -249,11 +249,14 @@ __device__ void form_A(WarpShared<T, N, QC>& ws, int nr, int lane, T* bcol) {   
     const int j = ee - i * (i + 1) / 2;
     const T* wi = ws.W[i];
     const T* wj = ws.W[j];
-    T a0 = 0, a1 = 0;
+    T a0 = 0, a1 = 0, a2 = 0, a3 = 0;
 #pragma unroll
-    for (int k = 0; k + 1 < NW; k += 2) { a0 += wi[k] * wj[k]; a1 += wi[k + 1] * wj[k + 1]; }
-    if (NW & 1) a0 += wi[NW - 1] * wj[NW - 1];
-    if (ok) ws.A[ee] = a0 + a1;
+    for (int k = 0; k + 3 < NW; k += 4) {
+      a0 += wi[k] * wj[k]; a1 += wi[k + 1] * wj[k + 1]; a2 += wi[k + 2] * wj[k + 2]; a3 += wi[k + 3] * wj[k + 3];
+    }
+#pragma unroll
+    for (int k = NW & ~3; k < NW; k++) a0 += wi[k] * wj[k];
+    if (ok) ws.A[ee] = (a0 + a2) + (a1 + a3);
   }
   if (bcol) {
 #pragma unroll 1

@@ -175,6 +175,16 @@ template <> __device__ __forceinline__ double sqrtT<double>(double x) { return s
 template <typename T> __device__ __forceinline__ T rsqrtT(T x);
 template <> __device__ __forceinline__ float rsqrtT<float>(float x) { float r = rsqrtf(x); return r * fmaf(fmaf(-x * r, r, 1.0f), 0.5f, 1.0f); }
 template <> __device__ __forceinline__ double rsqrtT<double>(double x) { return 1.0 / sqrt(x); }
+// 1 / x without the IEEE division's special-case subroutine: ncu r1 showed ptxas' slow path entered ~17 times per substep
+// by a third of the lanes (idle lanes, tiny pivots) and the whole warp waits for it. MUFU.RCP + one Newton step is
+// within an ulp for normal operands; FP64 keeps the exact division (the FP64 build is the parity check of the algorithm).
+template <typename T> __device__ __forceinline__ T rcpT(T x);
+template <> __device__ __forceinline__ float rcpT<float>(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return fmaf(r, fmaf(-x, r, 1.0f), r);
+}
+template <> __device__ __forceinline__ double rcpT<double>(double x) { return 1.0 / x; }
 template <typename T> __device__ __forceinline__ T absT(T x) { return x < 0 ? -x : x; }
 template <typename T> __device__ __forceinline__ T maxT(T a, T b) { return a > b ? a : b; }
 template <typename T> __device__ __forceinline__ T minT(T a, T b) { return a < b ? a : b; }

@@ -99,7 +99,7 @@ __device__ __forceinline__ void ldl_factor(const Topo<N>& tp, T* Mrow, T Mb, T& 
     // lanes outside the finger chains read a meaningless (often zero) pivot; their quotient is never used, but an
     // IEEE division by 0 / denormal sends the WHOLE warp through ptxas' slow-path subroutine (ncu r1: 12 such calls
     // per substep from this line alone), so they divide by one instead
-    T inv = T(1) / (tp.chain ? Dk : T(1));
+    T inv = rcpT<T>(tp.chain ? Dk : T(1));
     bool below = tp.chain && tp.local > k;
     T mk_pre = Mrow[k];
     T l = below ? mk_pre * inv : T(0);
@@ -115,10 +115,11 @@ __device__ __forceinline__ void ldl_factor(const Topo<N>& tp, T* Mrow, T Mb, T& 
 #pragma unroll
   for (int k = 0; k < NL; k++) if (tp.local == k) d = Mrow[k];
   const T dsafe = (tp.lane != 0 && tp.act) ? d : T(1);       // same reason: no special-case operands on idle lanes
-  T contrib = (tp.lane != 0 && tp.act) ? Mb * Mb / dsafe : T(0);
+  const T dinv = rcpT<T>(dsafe);
+  T contrib = (tp.lane != 0 && tp.act) ? Mb * Mb * dinv : T(0);
   T s = warp_sum(contrib);
   if (tp.lane == 0) { D = Mrow[0] - s; lb = 0; }
-  else { D = d; lb = tp.act ? Mb / dsafe : T(0); }
+  else { D = d; lb = tp.act ? Mb * dinv : T(0); }
 }
 
 // x <- L^-1 x (lane-distributed)
@@ -944,7 +945,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   }
   // Euler with implicit damping: (M + h D) a = tau + tau_c
   T x = ldl_fwd<T, N>(tp, M2row, lb2, tau + tauc);
-  x = tp.act ? x / (tp.act ? D2 : T(1)) : T(0);
+  x = tp.act ? x * rcpT<T>(tp.act ? D2 : T(1)) : T(0);
   {
     T xb = __shfl_sync(GMJ_FULL, x, 0);
     if (lane != 0 && tp.act) x -= lb2 * xb;

@@ -26,13 +26,14 @@ template <typename T> __device__ inline V3<T> support(const Shape<T>& s, V3<T> d
     p = mk<T>(dl.x >= 0 ? s.size.x : -s.size.x, dl.y >= 0 ? s.size.y : -s.size.y, dl.z >= 0 ? s.size.z : -s.size.z);
   } else if (s.type == GMJ_GEOM_CYLINDER) {
     T l = sqrtT<T>(dl.x * dl.x + dl.y * dl.y);
-    if (l > T(1e-12)) { p.x = s.size.x * dl.x / l; p.y = s.size.x * dl.y / l; } else { p.x = 0; p.y = 0; }
+    if (l > T(1e-12)) { const T rl = rcpT<T>(l); p.x = s.size.x * dl.x * rl; p.y = s.size.x * dl.y * rl; } else { p.x = 0; p.y = 0; }
     p.z = dl.z >= 0 ? s.size.z : -s.size.z;
   } else {
     T a = s.size.x, b = s.size.y, c = s.size.z;
     T l = sqrtT<T>(a * a * dl.x * dl.x + b * b * dl.y * dl.y + c * c * dl.z * dl.z);
     if (l < T(1e-30)) l = T(1e-30);
-    p = mk<T>(a * a * dl.x / l, b * b * dl.y / l, c * c * dl.z / l);
+    const T rl = rcpT<T>(l);
+    p = mk<T>(a * a * dl.x * rl, b * b * dl.y * rl, c * c * dl.z * rl);
   }
   if (s.round > 0) p = p + dl * s.round;
   return mul(s.R, p) + s.pos;
@@ -62,7 +63,7 @@ template <typename T> __device__ inline void tri_closest_origin(V3<T> a, V3<T> b
   if (vb <= 0 && d2 >= 0 && d6 <= 0) { T v = d2 / (d2 - d6); w[0] = 1 - v; w[1] = 0; w[2] = v; return; }
   T va = d3 * d6 - d5 * d4;
   if (va <= 0 && (d4 - d3) >= 0 && (d5 - d6) >= 0) { T v = (d4 - d3) / ((d4 - d3) + (d5 - d6)); w[0] = 0; w[1] = 1 - v; w[2] = v; return; }
-  T den = T(1) / (va + vb + vc);
+  T den = rcpT<T>(va + vb + vc);
   w[1] = vb * den; w[2] = vc * den; w[0] = 1 - w[1] - w[2];
 }
 
@@ -121,7 +122,7 @@ __device__ GMJ_CINL int mpr_penetration(const Shape<T>& A, const Shape<T>& B, T*
   V3<T> p = v1.v * w[0] + v2.v * w[1] + v3.v * w[2];
   *pos = ((v1.a + v1.b) * w[0] + (v2.a + v2.b) * w[1] + (v3.a + v3.b) * w[2]) * T(0.5);
   T d = sqrtT<T>(dot(p, p));
-  if (d > T(1e-12)) *normal = p * (T(1) / d);
+  if (d > T(1e-12)) *normal = p * rcpT<T>(d);
   else {
     V3<T> nn = normalized(cross(v2.v - v1.v, v3.v - v1.v));
     if (dot(nn, v0.v) > 0) nn = nn * T(-1);
@@ -164,7 +165,7 @@ __device__ GMJ_CINL int plane_candidates(const Shape<T>& s, T gz, V3<T>* pts, T*
     V3<T> vec = mk<T>(-axis.x * prj, -axis.y * prj, T(-1) - axis.z * prj);
     T len = sqrtT<T>(dot(vec, vec));
     if (len < T(1e-12)) { vec = mk<T>(s.R.m[0], s.R.m[3], s.R.m[6]); len = 1; }
-    vec = vec * (s.size.x / len);
+    vec = vec * (s.size.x * rcpT<T>(len));
     V3<T> ax = axis * s.size.z;
     V3<T> p = s.pos + ax + vec; p.z -= s.round; pts[n] = p; d[n] = p.z - gz; n++;
     p = s.pos - ax + vec; p.z -= s.round; pts[n] = p; d[n] = p.z - gz; n++;

@@ -620,7 +620,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   T D, lb, D2, lb2;
   ldl_factor<T, N>(tp, Mrow, Mb, D, lb);
   ldl_factor<T, N>(tp, M2row, Mb, D2, lb2);
-  const T rsq = tp.act ? T(1) / sqrtT<T>(D) : T(0);
+  const T rsq = tp.act ? rsqrtT<T>(tp.act ? D : T(1)) : T(0);
   int bad = !(D > 0) && tp.act;
   // second factor to shared memory for column access
   if (tp.chain) { int fi = (lane - 1) / NL;
@@ -885,7 +885,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   T pf[2], py[2], pb[2], pR[2], pinv[2]; int ptype[2];
   {
     T tc = maxT<T>(M.solref_tc, 2 * dt), dr = M.solref_dr, dmax = M.solimp[1];
-    T kk = T(1) / (dmax * dmax * tc * tc * dr * dr), bb = T(2) / (dmax * tc);
+    T kk = rcpT<T>(dmax * dmax * tc * tc * dr * dr), bb = T(2) * rcpT<T>(dmax * tc);
 #pragma unroll
     for (int slot = 0; slot < 2; slot++) {
       int r = slot ? r1 : r0;
@@ -899,10 +899,10 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
         if (type == ROW_CONTACT) {
           int rf = ws.rfirst[r]; T mu = ws.rmu[r];
           T Ann = T(0.25) * (ws.A[TRI(rf, rf)] + ws.A[TRI(rf + 1, rf + 1)] + 2 * ws.A[TRI(rf + 1, rf)]);
-          Rv = 2 * mu * mu * (1 - imp) / imp * (1 + mu * mu) * Ann;
-        } else Rv = (1 - imp) / imp * Arr;
+          Rv = 2 * mu * mu * (1 - imp) * rcpT<T>(imp) * (1 + mu * mu) * Ann;
+        } else Rv = (1 - imp) * rcpT<T>(imp) * Arr;
         Rv = maxT<T>(Rv, T(1e-15));
-        pR[slot] = Rv; pinv[slot] = T(1) / (Arr + Rv); pb[slot] = bcol[slot] - aref; ptype[slot] = type;
+        pR[slot] = Rv; pinv[slot] = rcpT<T>(Arr + Rv); pb[slot] = bcol[slot] - aref; ptype[slot] = type;
         pf[slot] = (e.nrow_prev == nr) ? e.fprev[r] : T(0);
       }
     }

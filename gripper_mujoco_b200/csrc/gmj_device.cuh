@@ -203,7 +203,7 @@ template <typename T> __device__ __forceinline__ M3<T> rot_axis(V3<T> a, T t) {
 }
 template <typename T> __device__ __forceinline__ V3<T> normalized(V3<T> a) {
   T l = sqrtT<T>(dot(a, a));
-  return l > 0 ? a * rcpT<T>(l) : a;
+  return l > T(1e-30) ? a * rcpT<T>(l) : a;      // (a denormal length flushes to zero in rcp.approx.ftz)
 }
 template <typename T> __device__ __forceinline__ T warp_sum(T v) {
 #pragma unroll

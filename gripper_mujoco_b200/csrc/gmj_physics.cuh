@@ -178,12 +178,12 @@ __device__ __forceinline__ T ldl_mulL(const Topo<N>& tp, const T* Lrow, T lb, T 
 
 template <typename T> __device__ __forceinline__ T impedance(const T* solimp, T pos) {
   T d0 = solimp[0], dw = solimp[1], width = solimp[2], mid = solimp[3], power = solimp[4];
-  T x = absT<T>(pos) / width;
+  T x = absT<T>(pos) * rcpT<T>(width);
   if (x >= 1) return dw;
   if (x <= 0) return d0;
   T y;
   // power = 2 in every model of the reference (solimp "0.9 0.95 0.001 0.5 2"): no powf expansion on the hot path
-  T a = (x <= mid) ? x / mid : (1 - x) / (1 - mid);
+  T a = (x <= mid) ? x * rcpT<T>(mid) : (1 - x) * rcpT<T>(1 - mid);
   T ap = (power == T(2)) ? a * a : powT<T>(a, power);
   if (x <= mid) y = ap * mid;
   else y = 1 - ap * (1 - mid);
@@ -963,7 +963,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   if (has_obj) {
     T ao[6];
 #pragma unroll
-    for (int k = 0; k < 6; k++) { T gk = __shfl_sync(GMJ_FULL, go, k); ao[k] = (tauo[k] + gk / rsqo[k]) / Mo[k]; bad |= !(absT<T>(ao[k]) < T(1e10)); }
+    for (int k = 0; k < 6; k++) { T gk = __shfl_sync(GMJ_FULL, go, k); ao[k] = (tauo[k] + gk * rcpT<T>(rsqo[k])) * rcpT<T>(Mo[k]); bad |= !(absT<T>(ao[k]) < T(1e10)); }
     if (lane == 0) {
       V3<T> vo = mk<T>(e.qvel[32], e.qvel[33], e.qvel[34]), wo = mk<T>(e.qvel[35], e.qvel[36], e.qvel[37]);
       vo = vo + mk<T>(ao[0], ao[1], ao[2]) * dt; wo = wo + mk<T>(ao[3], ao[4], ao[5]) * dt;

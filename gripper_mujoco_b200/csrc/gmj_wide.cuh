@@ -136,7 +136,7 @@ __device__ __forceinline__ void ldl_factor_w(WideShared<T, N>& ws, int& xn, cons
     T* col = ws.colb[tp.w][k & 1];
     col[tp.lane] = row[k];
     __syncwarp();
-    const T inv = T(1) / col[k];
+    const T inv = rcpT<T>(col[k]);
     const T Mbk = __shfl_sync(GMJ_FULL, Mb, k);
     const bool below = tp.chain && tp.local > k;
     const T mk_pre = below ? row[k] : T(0);
@@ -159,10 +159,11 @@ __device__ __forceinline__ void ldl_factor_w(WideShared<T, N>& ws, int& xn, cons
     if (tp.chain && k <= tp.local) Lw[tp.local * NLP + k] = row[k];
     if (tp.chain && k == tp.local) d = row[k];
   }
-  T s[1] = { (tp.chain || tp.palm) ? Mb * Mb / d : T(0) };
+  const T dinv = rcpT<T>((tp.chain || tp.palm) ? d : T(1));
+  T s[1] = { (tp.chain || tp.palm) ? Mb * Mb * dinv : T(0) };
   xsum<T, N, 1>(ws, xn, tp.w, tp.lane, s);
   if (tp.base) { D = dself - s[0]; lb = 0; }
-  else { D = d; lb = (tp.chain || tp.palm) ? Mb / d : T(0); }
+  else { D = d; lb = (tp.chain || tp.palm) ? Mb * dinv : T(0); }
 }
 
 // point Jacobian entry of this thread's dof for a point p on the gripper body in slot `bs`, along d
@@ -395,7 +396,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
 #pragma unroll
   for (int k = 0; k < NL; k++) if (tp.chain && k == tp.local) Mrow[k] += dt * damp;
   ldl_factor_w<T, N>(ws, xn, tp, Mrow, L2w, Mb, Mself + dt * damp, D2, lb2);
-  const T rsq = tp.act ? T(1) / sqrtT<T>(D) : T(0);
+  const T rsq = tp.act ? rsqrtT<T>(tp.act ? D : T(1)) : T(0);
   int bad = !(D > 0) && tp.act;
   // whitened smooth force w_s = D^-1/2 L^-1 tau
   T wsm;
@@ -669,7 +670,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
     }
     T pf[2], pb[2], pR[2]; int ptype[2];
     T tc = maxT<T>(M.solref_tc, 2 * dt), dr = M.solref_dr, dmax = M.solimp[1];
-    T kk = T(1) / (dmax * dmax * tc * tc * dr * dr), bb = T(2) / (dmax * tc);
+    T kk = rcpT<T>(dmax * dmax * tc * tc * dr * dr), bb = T(2) * rcpT<T>(dmax * tc);
 #pragma unroll
     for (int slot = 0; slot < 2; slot++) {
       int r = slot ? r1 : r0;
@@ -683,8 +684,8 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
         if (type == ROW_CONTACT) {
           int rf = ws.rfirst[r]; T mu = ws.rmu[r];
           T Ann = T(0.25) * (ws.A[TRI(rf, rf)] + ws.A[TRI(rf + 1, rf + 1)] + 2 * ws.A[TRI(rf + 1, rf)]);
-          Rv = 2 * mu * mu * (1 - imp) / imp * (1 + mu * mu) * Ann;
-        } else Rv = (1 - imp) / imp * Arr;
+          Rv = 2 * mu * mu * (1 - imp) * rcpT<T>(imp) * (1 + mu * mu) * Ann;
+        } else Rv = (1 - imp) * rcpT<T>(imp) * Arr;
         Rv = maxT<T>(Rv, T(1e-15));
         pR[slot] = Rv; pb[slot] = bcol[slot] - aref; ptype[slot] = type;
         pf[slot] = (e.nrow_prev == nr) ? e.fprev[r] : T(0);
@@ -736,7 +737,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
   // Euler with implicit damping: (M + h D) a = tau + tau_c
   T x;
   { T x1[1] = { tp.act ? tau + tauc : T(0) }; fwd_w<T, N, 1, 0>(ws, xn, tp, L2w, lb2, x1, nullptr); x = x1[0]; }
-  x = tp.act ? x / (tp.act ? D2 : T(1)) : T(0);
+  x = tp.act ? x * rcpT<T>(tp.act ? D2 : T(1)) : T(0);
   {
     T xb = __shfl_sync(GMJ_FULL, x, TW::BASE_L);
     if (tp.chain || tp.palm) x -= lb2 * xb;
@@ -753,7 +754,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
     if (has_obj) {
       T ao[6];
 #pragma unroll
-      for (int k = 0; k < 6; k++) { T gk = __shfl_sync(GMJ_FULL, go, k); ao[k] = (tauo[k] + gk / rsqo[k]) / Mo[k]; bad |= !(absT<T>(ao[k]) < T(1e10)); }
+      for (int k = 0; k < 6; k++) { T gk = __shfl_sync(GMJ_FULL, go, k); ao[k] = (tauo[k] + gk * rcpT<T>(rsqo[k])) * rcpT<T>(Mo[k]); bad |= !(absT<T>(ao[k]) < T(1e10)); }
       if (lane == 0) {
         vo = vo + mk<T>(ao[0], ao[1], ao[2]) * dt; wo = wo + mk<T>(ao[3], ao[4], ao[5]) * dt;
         e.qvel[OQ] = vo.x; e.qvel[OQ + 1] = vo.y; e.qvel[OQ + 2] = vo.z; e.qvel[OQ + 3] = wo.x; e.qvel[OQ + 4] = wo.y; e.qvel[OQ + 5] = wo.z;

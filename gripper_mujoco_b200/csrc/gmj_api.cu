@@ -354,6 +354,7 @@ static int build_settings(const GmjSettings* s, DevSettings* d) {
   // asking for the observation is an error (launch_step)
   d->obs_ok = !(deep || no > GMJ_MAX_OBS);
   d->n_obs = no;
+  for (int k = 0; k < GSEN_COUNT; k++) { const float rr = (float)s->sensor[k][GSF_read_rate]; d->read_between[k] = (double)(1 / rr); }
   return 0;
 }
 

@@ -92,6 +92,7 @@ struct DevSettings {
   int prev_steps[GSEN_COUNT], readings_per_step[GSEN_COUNT];
   int n_obs;
   int obs_ok;   // 0: the sensor history asked for is deeper than the device ring (observation unavailable)
+  double read_between[GSEN_COUNT];   // (double)(1.0f / (float)read_rate) per sensor: MjType::Sensor::ready_to_read's interval
   const double* asin_tab;   // asin(G_XY_STEP d / G_LEADSCREW), d in [-G_TH_TAB, G_TH_TAB] (stepper ticks, gmj_tail.cuh)
 };
 

@@ -180,8 +180,7 @@ __device__ inline float apply_noise(EnvState<T, QC>& e, const DevSettings& S, in
   return value;
 }
 template <typename T, int QC> __device__ inline int ready_to_read(EnvState<T, QC>& e, const DevSettings& S, int sensor, int slot) { // src/mjclass.h:225-241
-  float rr = (float)S.s.sensor[sensor][GSF_read_rate];
-  double between = 1 / rr;
+  const double between = S.read_between[sensor];       // = (double)(1 / (float)read_rate), formed once on the host
   if (e.time > e.last_read_time[slot] + between) { e.last_read_time[slot] = e.time; return 1; }
   return 0;
 }
@@ -375,7 +374,7 @@ __device__ inline void update_all(EnvState<T, QC>& e, const T* qfk, const double
   }
   if (e.has_object) {
     T vx = e.qvel[QC - 8], vy = e.qvel[QC - 7], vz = e.qvel[QC - 6];
-    if (sqrt((double)vx * vx + (double)vy * vy + (double)vz * vz) < 1e-6)
+    if ((double)vx * vx + (double)vy * vy + (double)vz * vz < 1e-12)          // |v| < 1e-6 without the FP64 square root
       for (int k = 0; k < 6; k++) e.qvel[QC - 8 + k] = 0;
   }
 }

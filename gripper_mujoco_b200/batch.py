@@ -153,6 +153,14 @@ class GripperBatch:
         check(self.L.gmj_probe_host(self.h, p.ctypes.data_as(C.c_void_p)))
         return p
 
+    def probe_noalloc(self, out: np.ndarray | None = None):
+        """gmj_probe_host_noalloc: the same probe through the library's static device scratch -- no cudaMalloc /
+        cudaFree, n_envs <= GMJ_NOALLOC_MAX_ENVS (16384). `out`: caller-owned float64 [n_envs, GMJ_PROBE_LEN] buffer."""
+        torch.cuda.synchronize(self.device)
+        p = np.zeros((self.n_envs, GMJ_PROBE_LEN)) if out is None else out
+        check(self.L.gmj_probe_host_noalloc(self.h, p.ctypes.data_as(C.c_void_p)))
+        return p
+
     def probe_field(self, name):
         return self.probe()[:, GP[name]]
 

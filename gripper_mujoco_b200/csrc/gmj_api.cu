@@ -586,6 +586,40 @@ int gmj_probe_host(GmjHandle* h, double* probe_host) {
   return 0;
 }
 
+// ------------------------------------------------------------------ allocation-free probe
+// Scratch of gmj_probe_host_noalloc: lives in the library image (every GPU that loads the library holds these 4 MiB
+// until exit), shared by every call and every handle on a device -- calls that overlap on the GPU race on it.
+static __device__ __align__(256) double g_noalloc_scratch[(size_t)GMJ_NOALLOC_MAX_ENVS * GMJ_PROBE_LEN];
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is looked up
+// once per device, with that device current, and cached here.
+#define GMJ_NOALLOC_MAX_DEVICES 64
+static double* g_noalloc_ptr[GMJ_NOALLOC_MAX_DEVICES];
+
+int gmj_probe_host_noalloc(GmjHandle* h, double* probe_host) {
+  if (!h || !probe_host) FAIL("null argument");
+  if (h->n_envs > GMJ_NOALLOC_MAX_ENVS)
+    FAIL("gmj_probe_host_noalloc: n_envs = " + std::to_string(h->n_envs) + " exceeds the static scratch (GMJ_NOALLOC_MAX_ENVS = " +
+         std::to_string(GMJ_NOALLOC_MAX_ENVS) + "); use gmj_probe_host");
+  if (h->device < 0 || h->device >= GMJ_NOALLOC_MAX_DEVICES) FAIL("gmj_probe_host_noalloc: device index out of range");
+  CK(cudaSetDevice(h->device));
+  if (!g_noalloc_ptr[h->device]) {
+    double* ptr = nullptr;
+    CK(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+    g_noalloc_ptr[h->device] = ptr;
+  }
+  double* scratch = g_noalloc_ptr[h->device];
+  const size_t n = (size_t)h->n_envs * GMJ_PROBE_LEN;
+  int tb = 128, nb = (h->n_envs + tb - 1) / tb;
+  // k_dump zeroes every probe row before filling it, so nothing of the previous call survives in the rows read back
+  GMJ_FOR_STATE(h, k_dump<T, QC><<<nb, tb>>>((const EnvState<T, QC>*)h->envs, h->n_envs, h->B, nullptr, nullptr, scratch));
+#define GMJ_GAUGE(NN) GMJ_FOR_STATE(h, k_gauge<T, NN, QC><<<nb, tb>>>((const EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->n_envs, scratch))
+  switch (h->N) { case 5: GMJ_GAUGE(5); break; case 8: GMJ_GAUGE(8); break; case 16: GMJ_GAUGE(16); break; case 24: GMJ_GAUGE(24); break; default: break; }
+#undef GMJ_GAUGE
+  CK(cudaGetLastError());
+  CK(cudaMemcpy(probe_host, scratch, n * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
 int gmj_stats(GmjHandle* h, GmjStats* out) {
   if (!h || !out) FAIL("null argument");
   CK(cudaSetDevice(h->device));

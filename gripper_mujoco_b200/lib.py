@@ -19,6 +19,7 @@ SOURCES = ["gmj_api.cu", "gmj_inst.cu", "gmj_step.cuh", "gmj_wide.cuh", "gmj_phy
 HEADERS = [os.path.join(_HERE, "..", "include", h) for h in ("gmj.h", "gmj_types.h")]
 
 GMJ_PROBE_LEN = 32
+GMJ_NOALLOC_MAX_ENVS = 16384      # include/gmj.h: static scratch of gmj_probe_host_noalloc
 GMJ_EVENT_STATE_LEN = 57
 PROBE_FIELDS = ["time", "wrist_z", "gauge0", "gauge1", "gauge2", "si_gauge0", "si_gauge1", "si_gauge2",
                 "si_palm", "si_wrist", "ncon", "nrow", "niter", "unstable", "weld_on", "base_z",
@@ -29,7 +30,7 @@ GP = {n: i for i, n in enumerate(PROBE_FIELDS)}
 # every symbol include/gmj.h declares (tests check the .so exports exactly these)
 SYMBOLS = ["gmj_create", "gmj_destroy", "gmj_set_settings", "gmj_set_objects", "gmj_reset", "gmj_spawn",
            "gmj_step", "gmj_set_action", "gmj_action_step", "gmj_substeps", "gmj_observe", "gmj_n_obs",
-           "gmj_n_actions", "gmj_n_envs", "gmj_get_state_host", "gmj_probe_host", "gmj_stats",
+           "gmj_n_actions", "gmj_n_envs", "gmj_get_state_host", "gmj_probe_host", "gmj_probe_host_noalloc", "gmj_stats",
            "gmj_set_welds", "gmj_last_error"]
 
 
@@ -131,6 +132,7 @@ def lib():
         getattr(L, f).argtypes = [vp]
     L.gmj_get_state_host.argtypes = [vp, vp, vp]
     L.gmj_probe_host.argtypes = [vp, vp]
+    L.gmj_probe_host_noalloc.argtypes = [vp, vp]
     L.gmj_stats.argtypes = [vp, C.POINTER(GmjStats)]
     L.gmj_set_welds.argtypes = [vp, i32, vp]
     _LIB = L

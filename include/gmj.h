@@ -77,6 +77,13 @@ enum { GP_time = 0, GP_wrist_z, GP_gauge0, GP_gauge1, GP_gauge2, GP_si_gauge0, G
        GP_cumulative_reward, GP_has_object, GP_obj_index, GP_episode, GP_last_reward, GP_last_done,
        GMJ_PROBE_LEN = 32 };
 int gmj_probe_host(GmjHandle* h, double* probe_host);
+/* Allocation-free variant of gmj_probe_host. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it). The device scratch is a static 4 MiB array inside the library (held by every GPU that loads it, until exit),
+ * so n_envs <= GMJ_NOALLOC_MAX_ENVS; larger handles are rejected with an error. It calls no cudaMalloc / cudaFree. All
+ * calls on a device share the array: calls that overlap on the GPU race; results equal gmj_probe_host's. */
+#define GMJ_NOALLOC_MAX_ENVS 16384
+int gmj_probe_host_noalloc(GmjHandle* h, double* probe_host);
 int gmj_stats(GmjHandle* h, GmjStats* out);
 /* overwrite joint positions of all envs with qpos (host, double[nq]) and zero velocities: used by the
  * calibration flow (calibrate_reset writes qpos directly, src/myfunctions.cpp:1497-1516) */

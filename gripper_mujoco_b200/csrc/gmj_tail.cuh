@@ -296,7 +296,7 @@ __device__ inline void monitor_sensors(EnvState<T, QC>& e, const DevSettings& S,
   if (due) {
     for (int f = 0; f < 3; f++) {
       float gv = f == 0 ? gfit0 : (f == 1 ? gfit1 : gfit2);
-      e.si_latest[f] = (float)(gv * (float)g[GS_sim_gauge_raw_to_N_factor]);
+      e.si_latest[f] = (float)((double)gv * g[GS_sim_gauge_raw_to_N_factor]);   // gfloat * double member (src/mjclass.cpp:755-757)
       gv = apply_normalisation(S.s.sensor[GSEN_bending_gauge], gv);
       gv = apply_noise(e, S, GSEN_bending_gauge, gv, f + 1);
       win_add(e, ST_gauge + f, gv);

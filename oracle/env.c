@@ -182,6 +182,14 @@ typedef struct {
 static void extract_forces(const OrEnv* e, OrForces* F) {
   memset(F, 0, sizeof(*F));
   if (!e->has_object) return;                      /* live_objects.size() == 0 -> empty */
+  if (e->script) {
+    const double* c = e->script_cur;
+    for (int k = 0; k < 3; k++) {
+      for (int f = 0; f < 3; f++) { F->all_f_loc[f][k] = c[3 + 3 * f + k]; F->obj_f_loc[f][k] = c[15 + 3 * f + k]; F->gnd_f_loc[f][k] = c[30 + 3 * f + k]; }
+      F->all_palm_loc[k] = c[12 + k]; F->obj_palm_loc[k] = c[24 + k]; F->obj_gnd[k] = c[27 + k];
+    }
+    return;
+  }
   for (int c = 0; c < e->ncon; c++) {
     const OrContact* cn = &e->con[c];
     int a = cn->cls1, b = cn->cls2;
@@ -215,8 +223,8 @@ static void monitor_sensors(OrEnv* e) {
   const double* g = e->s.general;
   if (ready_to_read(e, GSEN_bending_gauge)) {
     for (int f = 0; f < 3; f++) {
-      float gv = or_read_gauge(e, f);
-      or_win_add(&e->si_gauge[f], (float)(gv * (float)g[GS_sim_gauge_raw_to_N_factor]));
+      float gv = e->script ? (float)e->script_cur[f] : or_read_gauge(e, f);
+      or_win_add(&e->si_gauge[f], (float)((double)gv * g[GS_sim_gauge_raw_to_N_factor]));   /* gfloat * double member, src/mjclass.cpp:755-757 */
       gv = apply_normalisation(e->s.sensor[GSEN_bending_gauge], gv);
       gv = apply_noise(e, GSEN_bending_gauge, gv, f + 1);
       or_win_add(&e->w_gauge[f], gv);
@@ -397,7 +405,76 @@ void or_spawn(OrEnv* e, const GmjObject* o, double x, double y, double zrot) {
   for (int k = 0; k < 6; k++) e->qvel[e->B + k] = 0;
   e->start_z = q[2];
   e->nrow_prev = 0;
+  if (e->script) { e->script_cur[40] = q[0]; e->script_cur[41] = q[1]; e->script_cur[42] = q[2]; return; }
   or_forward(e);
+}
+
+/* ------------------------------------------------------------------ spawn_into_scene (src/mjclass.cpp:2475-2654)
+ * Fingertip boxes as Env::reset takes them right after luke::reset (src/mjclass.h:893-904,
+ * luke::get_finger_hook_locations src/myfunctions.cpp:3717-3761): target at home, base at the origin. */
+static void fingertip_boxes(const OrEnv* e, double tips[3][8]) {
+  OrGripper home; or_gripper_reset(&home);
+  const double hook_th = e->m.hook_angle_deg * (M_PI / 180.000);
+  const double PI_23 = M_PI * (2.0 / 3.0);
+  for (int i = 0; i < 3; i++) {
+    double ang = i * PI_23;
+    double hook_x = 0.5 * e->m.hook_length * sin(hook_th);
+    double px = -(home.x - hook_x) * sin(ang) + 0.0, py = -(home.x - hook_x) * cos(ang) + 0.0;
+    or_box2d_init(tips[i], px, py, e->m.finger_width, e->m.hook_length, -ang);
+  }
+}
+/* the accept test of ONE candidate pose (:2594-2640): outer bounds (SpawnParams defaults +-100 m), then Box2d SAT with
+ * a 1 mm gap against the three fingertip boxes; single live object, so no object-object test */
+int or_spawn_ok(const OrEnv* e, double x, double y, double rot, const double* bbox) {
+  double ours[8], tips[3][8];
+  or_box2d_init(ours, x, y, bbox[0], bbox[1], rot);
+  for (int i = 0; i < 4; i++) if (ours[i] < -100 || ours[i] > 100 || ours[4 + i] < -100 || ours[4 + i] > 100) return 0;
+  fingertip_boxes(e, tips);
+  for (int i = 0; i < 3; i++) if (or_box2d_overlap(ours, tips[i], 1e-3)) return 0;
+  return 1;
+}
+/* Candidate grid (2 mm steps within +-xrange / +-yrange, pi/30 steps within +-rotrange), both lists shuffled, walked
+ * pairwise for max(n_xy, n_rot) tries, first accepted pose spawns; 0 when none is (the caller retries,
+ * rl/env/MjEnv.py:1216-1244). std::shuffle on the global engine becomes a Fisher-Yates walk on the counter RNG
+ * (same on the device): j = (int)(u * (i + 1)) for i = n-1 .. 1. */
+#define OR_SPAWN_MAXXY 1024
+#define OR_SPAWN_MAXROT 128
+static void fy_shuffle(OrEnv* e, unsigned short* a, int n) {
+  for (int i = n - 1; i >= 1; i--) {
+    int j = (int)(or_uniform(e) * (float)(i + 1)); if (j > i) j = i;
+    unsigned short t = a[i]; a[i] = a[j]; a[j] = t;
+  }
+}
+int or_spawn_into_scene(OrEnv* e, const GmjObject* o, double xpos, double ypos, double zrot, double xrange, double yrange,
+                        double rotrange) {
+  const double inc = 2e-3, rinc = M_PI / 30.0;
+  int num_x = (int)((2 * xrange) / inc) + 1, num_y = (int)((2 * yrange) / inc) + 1, num_r = (int)((2 * rotrange) / rinc) + 1;
+  int nxy = num_x * num_y;
+  if (nxy > OR_SPAWN_MAXXY || num_r > OR_SPAWN_MAXROT) return -1;
+  unsigned short pxy[OR_SPAWN_MAXXY], pr[OR_SPAWN_MAXROT];
+  for (int i = 0; i < nxy; i++) pxy[i] = (unsigned short)i;
+  for (int i = 0; i < num_r; i++) pr[i] = (unsigned short)i;
+  if (nxy > 1) fy_shuffle(e, pxy, nxy);
+  if (num_r > 1) fy_shuffle(e, pr, num_r);
+  int tries = nxy > num_r ? nxy : num_r;
+  for (int i = 0; i < tries; i++) {
+    int k = pxy[i % nxy], ix = k / num_y, iy = k % num_y, ir = pr[i % num_r];
+    double x = num_x > 1 ? -xrange + ix * inc + xpos : xpos;
+    double y = num_y > 1 ? -yrange + iy * inc + ypos : ypos;
+    double r = num_r > 1 ? -rotrange + ir * rinc + zrot : zrot;
+    if (or_spawn_ok(e, x, y, r, o->bbox)) { or_spawn(e, o, x, y, r); return 1; }
+  }
+  return 0;
+}
+/* object index draw of the batched env (device: same draw, before the pose search) */
+int or_draw_object(OrEnv* e, int n_objects) {
+  int oi = (int)(or_uniform(e) * n_objects); if (oi >= n_objects) oi = n_objects - 1;
+  return oi;
+}
+
+void or_set_script(OrEnv* e, const double* rows, int nrows) {
+  e->script = rows; e->script_rows = nrows; e->script_cursor = 0;
+  memset(e->script_cur, 0, sizeof(e->script_cur));
 }
 
 /* base target clamp shared by move_base_target_m / lift_base_to_height (src/myfunctions.cpp:2444-2529) */

@@ -26,6 +26,7 @@ extern "C" {
 
 #define OR_MAXV (GMJ_MAXB + 6)
 #define OR_MAXROW (6 * 7 + GMJ_MAXB + 4 * GMJ_MAXCON)
+#define OR_SCRIPT_ROWLEN 46         /* gauges 3 | all f1-3 loc 9 | all palm loc 3 | obj f1-3 loc 9 | obj palm loc 3 | obj gnd 3 | gnd f1-3 loc 9 | wrist z | obj xyz 3 | spare 3 */
 #define OR_WIN 16                 /* ring depth kept (reference keeps 1000, reads <= 7) */
 
 /* luke::Gripper (src/gripper.h:13-110) */
@@ -98,6 +99,11 @@ typedef struct OrEnv {
   uint64_t seed; uint32_t env_id; uint32_t rng_ctr;
   /* stats */
   int64_t st_substeps, st_contacts, st_rows, st_iters, st_unstable;
+  /* scripted physics observables (tests/test_ref_tail.py): when set, or_physics_step only advances the clock and
+   * loads the next row, and the tail reads gauges / force sums / wrist force / object position from it -- the same
+   * rows oracle/ref_tail_shim.cpp feeds to the reference's own compiled MjClass */
+  const double* script; int script_rows, script_cursor;
+  double script_cur[OR_SCRIPT_ROWLEN];
 } OrEnv;
 
 /* ---- gripper motor space (src/gripper.h, src/gripper.cpp) */
@@ -142,6 +148,10 @@ float or_read_gauge(const OrEnv* e, int finger);   /* read_armadillo_gauge */
 void or_forward(OrEnv* e);                 /* FK + collision only (mj_forward subset) */
 void or_set_weld(OrEnv* e, int id, int on);
 int or_struct_size(void);
+int or_spawn_ok(const OrEnv* e, double x, double y, double rot, const double* bbox3);
+int or_spawn_into_scene(OrEnv* e, const GmjObject* o, double x, double y, double zrot, double xrange, double yrange, double rotrange);
+int or_draw_object(OrEnv* e, int n_objects);
+void or_set_script(OrEnv* e, const double* rows, int nrows);
 
 #ifdef __cplusplus
 }

@@ -261,6 +261,16 @@ void or_physics_step(OrEnv* e) {
 
   /* after a BADQACC-class failure the env is frozen until reset (is_done reports it) */
   if (e->unstable) { e->time += dt; return; }
+  if (e->script) {                 /* scripted observables: the clock advances as in mj_step, nothing is simulated */
+    e->time += dt;
+    if (e->script_cursor < e->script_rows) {
+      memcpy(e->script_cur, e->script + (size_t)e->script_cursor * OR_SCRIPT_ROWLEN, sizeof(e->script_cur));
+      e->script_cursor++;
+    }
+    e->wrist_z = e->script_cur[39];
+    if (e->has_object) for (int k = 0; k < 3; k++) e->qpos[B + k] = e->script_cur[40 + k];
+    return;
+  }
   /* ---- mj_step1: position + velocity stage */
   or_kinematics(e);
   dynamics(e, M, bias);

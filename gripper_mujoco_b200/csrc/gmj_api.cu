@@ -219,6 +219,15 @@ __global__ void k_stats(const EnvState<T, QC>* envs, int n_envs, unsigned long l
   atomicAdd(&out[5], (unsigned long long)e.st_overflow);
 }
 
+#ifdef GMJ_PROF
+template <typename T, int QC>
+__global__ void k_prof(EnvState<T, QC>* envs, int n_envs, unsigned int* out, int clear) {
+  int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= n_envs) return;
+  for (int k = 0; k < 12; k++) { out[(size_t)env * 12 + k] = envs[env].prof[k]; if (clear) envs[env].prof[k] = 0; }
+}
+#endif
+
 // ------------------------------------------------------------------------------------------ host side
 
 static void quat2mat_h(const double* q, double* R) {
@@ -451,6 +460,7 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
     CK(cudaMalloc(&h->asin_tab, tab.size() * sizeof(double)));
     CK(cudaMemcpy(h->asin_tab, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice));
   }
+  CK(cudaMalloc(&h->taps, (size_t)n_envs * GMJ_MAXTAP * (GMJ_TAP_HDR + 3 * model->N) * (precision == 0 ? sizeof(float) : sizeof(double))));
   CK(cudaMalloc(&h->err_flag, sizeof(int))); CK(cudaMemset(h->err_flag, 0, sizeof(int)));
   CK(cudaMalloc(&h->stats_dev, 8 * sizeof(unsigned long long)));
   CK(cudaMalloc(&h->env_list, sizeof(int) * (size_t)n_envs)); CK(cudaMalloc(&h->env_count, sizeof(int)));
@@ -464,7 +474,7 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
 int gmj_destroy(GmjHandle* h) {
   if (!h) return 0;
   cudaSetDevice(h->device);
-  cudaFree(h->envs); cudaFree(h->model); cudaFree(h->settings); cudaFree(h->err_flag); cudaFree(h->stats_dev); cudaFree(h->env_list); cudaFree(h->env_count); cudaFree(h->perm); cudaFree(h->hist); cudaFree(h->asin_tab);
+  cudaFree(h->envs); cudaFree(h->model); cudaFree(h->settings); cudaFree(h->err_flag); cudaFree(h->stats_dev); cudaFree(h->env_list); cudaFree(h->env_count); cudaFree(h->perm); cudaFree(h->hist); cudaFree(h->asin_tab); cudaFree(h->taps);
   if (h->objects) cudaFree(h->objects);
   if (h->scratch) cudaFree(h->scratch);
   delete h;
@@ -619,6 +629,23 @@ int gmj_probe_host_noalloc(GmjHandle* h, double* probe_host) {
   CK(cudaMemcpy(probe_host, scratch, n * sizeof(double), cudaMemcpyDeviceToHost));
   return 0;
 }
+
+#ifdef GMJ_PROF
+// development build only: per-env cycle counters per phase, uint32[n_envs][12] to the host; clear != 0 zeroes them
+int gmj_prof_host(GmjHandle* h, unsigned int* out_host, int clear) {
+  if (!h || !out_host) FAIL("null argument");
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  unsigned int* d = nullptr;
+  CK(cudaMalloc(&d, sizeof(unsigned int) * 12 * (size_t)h->n_envs));
+  int tb = 128, nb = (h->n_envs + tb - 1) / tb;
+  GMJ_FOR_STATE(h, k_prof<T, QC><<<nb, tb>>>((EnvState<T, QC>*)h->envs, h->n_envs, d, clear));
+  CK(cudaGetLastError());
+  CK(cudaMemcpy(out_host, d, sizeof(unsigned int) * 12 * (size_t)h->n_envs, cudaMemcpyDeviceToHost));
+  CK(cudaFree(d));
+  return 0;
+}
+#endif
 
 int gmj_stats(GmjHandle* h, GmjStats* out) {
   if (!h || !out) FAIL("null argument");

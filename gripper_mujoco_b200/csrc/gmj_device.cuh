@@ -51,6 +51,9 @@ struct EnvState {
   unsigned long long st_contacts, st_rows, st_iters, st_substeps;
   unsigned int st_unstable, st_overflow, pending_extra, sort_key;   // pending_extra: lift substeps owed by set_action
   int mpr_prev;                     // MPR passes (0-2: finger plates, hooks) the last substep ran: load key of the lockstep sort
+#ifdef GMJ_PROF
+  unsigned int prof[12];            // development build: cycles per phase (gmj_physics.cuh GMJ_PROF_*)
+#endif
 };
 
 // model constants, lane-major [field][32] so a warp reads each field conflict-free

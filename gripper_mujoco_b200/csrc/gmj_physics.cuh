@@ -437,6 +437,21 @@ template <int NT> __device__ __forceinline__ void phase_idle() {
   for (int id = 0; id < GMJ_NPHASE; id++) phase_barrier<NT>(id);
 }
 
+// Development build -DGMJ_PROF: per-env cycle counters per phase (own work only; prof[10] = waits at the phase
+// barriers), read back by gmj_prof_host (profiles/r2_env_cost.py). prof[k] = cycles of the code between phase barrier k
+// and k + 1; prof[9] = per-substep tail; prof[11] = the whole substep loop.
+#ifdef GMJ_PROF
+#define GMJ_PROF_DECL long long prof_t0 = 0
+#define GMJ_PROF_END(k) do { if (lane == 0) e.prof[k] += (unsigned)(clock64() - prof_t0); } while (0)
+#define GMJ_PROF_BEGIN do { if (lane == 0) prof_t0 = clock64(); } while (0)
+#define GMJ_PHASE(k) do { GMJ_PROF_END((k) - 1); GMJ_PROF_BEGIN; phase_barrier<NT>(k); GMJ_PROF_END(10); GMJ_PROF_BEGIN; } while (0)
+#else
+#define GMJ_PROF_DECL
+#define GMJ_PROF_END(k)
+#define GMJ_PROF_BEGIN
+#define GMJ_PHASE(k) phase_barrier<NT>(k)
+#endif
+
 template <typename T, int N, int NT>
 __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, const DevSettings& S, int lane, double dtd, T tip_force) {
   const T dt = (T)dtd;
@@ -448,7 +463,8 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   const T gz = -M.zref;                                   // ground plane height in shifted coordinates
 
   // ------------------------------------------------------------------ kinematics
-  phase_barrier<NT>(0);
+  GMJ_PROF_DECL;
+  phase_barrier<NT>(0); GMJ_PROF_BEGIN;
   T q = tp.act ? e.qpos[lane] : T(0), qd = tp.act ? e.qvel[lane] : T(0);
   ws.qfk[lane] = q;
   M3<T> Rl; V3<T> pl = mk<T>(M.f[MF_pos0][lane], M.f[MF_pos1][lane], M.f[MF_pos2][lane]);
@@ -490,7 +506,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   const bool has_obj = e.has_object != 0;
 
   // ------------------------------------------------------------------ spatial quantities
-  phase_barrier<NT>(1);
+  GMJ_PHASE(1);
   T mass = tp.act ? M.f[MF_mass][lane] : T(0);
   V3<T> c = p + mul(R, mk<T>(M.f[MF_ip0][lane], M.f[MF_ip1][lane], M.f[MF_ip2][lane]));
   SpI<T> I;
@@ -563,7 +579,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   T Mb = (lane != 0 && tp.act) ? spdot(Sb, F) : T(0);
 
   // ------------------------------------------------------------------ control + smooth forces
-  phase_barrier<NT>(2);
+  GMJ_PHASE(2);
   // luke::control_gripper / control_base (src/myfunctions.cpp:1965-2057)
   T damp = tp.act ? M.f[MF_damp][lane] : T(0), stiff = tp.act ? M.f[MF_stiff][lane] : T(0);
   T ctrl = 0;
@@ -613,7 +629,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   __syncwarp();
 
   // ------------------------------------------------------------------ factorisations
-  phase_barrier<NT>(3);
+  GMJ_PHASE(3);
   T M2row[NL];
 #pragma unroll
   for (int k = 0; k < NL; k++) M2row[k] = Mrow[k] + ((k == tp.local && tp.act) ? dt * damp : T(0));
@@ -632,7 +648,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   __syncwarp();
 
   // ------------------------------------------------------------------ collision
-  phase_barrier<NT>(4);
+  GMJ_PHASE(4);
   int ncon = 0;
   Shape<T> so;
   so.type = (int)e.obj[0]; so.size = mk<T>(e.obj[1], e.obj[2], e.obj[3]); so.round = e.obj[4];
@@ -742,7 +758,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   __syncwarp();
 
   // ------------------------------------------------------------------ constraint rows
-  phase_barrier<NT>(5);
+  GMJ_PHASE(5);
   int nr = 0;
   const T zero6[6] = { 0, 0, 0, 0, 0, 0 };
   // Welds and joint limits act on ONE joint each: every such row is a multiple of L^-1 e_j, so the unit
@@ -875,7 +891,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   __syncwarp();
 
   // ------------------------------------------------------------------ A = W W^T (+ column W . w_s)
-  phase_barrier<NT>(6);
+  GMJ_PHASE(6);
   // lane owns rows r0 = lane and r1 = lane + 32
   const int r0 = lane, r1 = lane + 32;
   T bcol[2];
@@ -909,7 +925,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   }
   __syncwarp();
   // ------------------------------------------------------------------ dual LCP, direct
-  phase_barrier<NT>(7);
+  GMJ_PHASE(7);
   // (A + R) f + b = w, equality rows w = 0, inequality rows f >= 0, w >= 0, f w = 0. A + R is SPD so
   // the solution is unique: the oracle reaches it with PGS converged to 1e-13, here it is found by
   // block principal pivoting over the active set (warm-started from the previous substep) with an
@@ -922,7 +938,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   __syncwarp();
 
   // ------------------------------------------------------------------ constraint force, integration
-  phase_barrier<NT>(8);
+  GMJ_PHASE(8);
   T g = 0, go = 0;
   for (int r = 0; r < nr; r++) {
     T fr = e.fprev[r];
@@ -987,6 +1003,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
     for (int k = 0; k < 6; k++) (void)__shfl_sync(GMJ_FULL, go, k);
   }
   unsigned anybad = __ballot_sync(GMJ_FULL, bad);
+  GMJ_PROF_END(8);
   if (lane == 0) {
     if (anybad) e.unstable = 1;
     e.time += dtd;

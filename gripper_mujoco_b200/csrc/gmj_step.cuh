@@ -65,6 +65,7 @@ struct GmjHandle {
   GmjModel hm;
   size_t smem_bytes;
   double* asin_tab;      // device table for the stepper (DevSettings::asin_tab)
+  void* taps;            // T[n_envs][GMJ_MAXTAP][GMJ_TAP_HDR + 3 N]: sensor tap records of the running step (gmj_tail.cuh)
   int n_sm;              // SMs of the device
   int balance_sm;        // SM count when the combined launch balances envs per block over the SMs, 0 = full blocks
 };
@@ -93,7 +94,7 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
        int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
        float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,
        int* __restrict__ err_flag, int* __restrict__ env_list, int* __restrict__ env_count, int list_blocks,
-       const int* __restrict__ perm, int* __restrict__ hist, int bal_sm, int lift_wpb) {
+       const int* __restrict__ perm, int* __restrict__ hist, int bal_sm, int lift_wpb, T* __restrict__ tap_buf) {
   constexpr int WPB = StepCfg<T, N>::WPB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_nsub_max;
@@ -166,6 +167,11 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
     const double dtd = S.s.general[GS_mujoco_timestep];
     const bool curve = S.s.general[GS_curve_validation] != 0;
     const T tipf = curve ? (T)S.s.general[GS_tip_force_applied] : T(0);
+    T* const taps = tap_buf + (size_t)env * (GMJ_MAXTAP * (GMJ_TAP_HDR + 3 * N));
+    int ntap = 0;
+#ifdef GMJ_PROF
+    const long long prof_loop0 = clock64();
+#endif
     for (int i = 0; i < nsub_max; i++) {
       __syncthreads();                       // lockstep: shared instruction stream
       if (i < nsub) {
@@ -173,13 +179,24 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
         __syncwarp();
         physics_substep<T, N, 32 * WPB>(ws, M, S, lane, dtd, tipf);
         phase_barrier<32 * WPB>(GMJ_NPHASE);
+#ifdef GMJ_PROF
+        long long prof_t0 = clock64();
+#endif
         if (lane == 0) update_all<T, N>(e, ws.qfk, S.asin_tab);
         __syncwarp();
-        if (flags & STEP_SENSORS) monitor_sensors<T, N>(e, S, M, ws.ax, lane);
+        if (flags & STEP_SENSORS) sensor_taps<T, N>(e, S, M, ws.ax, taps, ntap, lane);
         __syncwarp();
+#ifdef GMJ_PROF
+        if (lane == 0) e.prof[9] += (unsigned)(clock64() - prof_t0);
+#endif
       } else { phase_idle<32 * WPB>(); phase_barrier<32 * WPB>(GMJ_NPHASE); }
     }
     if (valid && lane == 0) e.wrist_z = (float)ws.ax.wrist_z;
+#ifdef GMJ_PROF
+    if (valid && lane == 0) e.prof[11] += (unsigned)(clock64() - prof_loop0);
+#endif
+    // the taps of this launch, in time order, outside the lockstep loop (no other warp waits for the FP64 fits)
+    if (valid && ntap > 0) { __syncwarp(); process_taps<T, N>(e, S, M, taps, ntap, lane); }
   }
   if (!valid) return;
   if ((flags & STEP_TAIL) && lane == 0) {
@@ -216,7 +233,7 @@ int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, co
   const int bal_sm = combined ? h->balance_sm : 0;
   if (bal_sm > 0) blocks = bal_sm * ((3 * h->n_envs + bal_sm * WPB - 1) / (bal_sm * WPB));   // bound (every env lifting); surplus blocks exit at once
   k_step<T, N><<<blocks + list_blocks, 32 * WPB, smem, st>>>((EnvState<T>*)h->envs, (const DevModel<T>*)h->model, h->settings,
-      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks, h->perm, h->hist, bal_sm, LW);
+      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks, h->perm, h->hist, bal_sm, LW, (T*)h->taps);
   CK(cudaGetLastError());
   h->smem_bytes = smem;
   return 0;
@@ -234,7 +251,7 @@ k_step_wide(EnvState<T, GMJ_WQC>* __restrict__ envs, const DevModel<T, GMJ_WNT>*
             int n_envs, int flags, int nsub_override, const int32_t* __restrict__ actions, const float* __restrict__ frac,
             float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ events,
             int* __restrict__ err_flag, int* __restrict__ env_list, int* __restrict__ env_count, int list_blocks,
-            const int* __restrict__ perm, int* __restrict__ hist) {
+            const int* __restrict__ perm, int* __restrict__ hist, T* __restrict__ tap_buf) {
   constexpr int EPB = WideCfg<T, N>::EPB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_nsub_max;
@@ -292,6 +309,8 @@ k_step_wide(EnvState<T, GMJ_WQC>* __restrict__ envs, const DevModel<T, GMJ_WNT>*
     const double dtd = S.s.general[GS_mujoco_timestep];
     const bool curve = S.s.general[GS_curve_validation] != 0;
     const T tipf = curve ? (T)S.s.general[GS_tip_force_applied] : T(0);
+    T* const taps = tap_buf + (size_t)env * (GMJ_MAXTAP * (GMJ_TAP_HDR + 3 * N));
+    int ntap = 0;                            // (kept by warp 0 of the env)
     for (int i = 0; i < nsub_max; i++) {
       wide_phase<T, N>();                    // lockstep: one instruction stream for the EPB envs of the block
       if (i < nsub) {
@@ -301,13 +320,15 @@ k_step_wide(EnvState<T, GMJ_WQC>* __restrict__ envs, const DevModel<T, GMJ_WNT>*
         env_sync<T, N>(ws);
         if (tid == 0) update_all<T, N>(e, ws.qfk, S.asin_tab);
         env_sync<T, N>(ws);
-        if ((flags & STEP_SENSORS) && warp == 0) monitor_sensors<T, N>(e, S, M, ws.ax, lane);
+        if ((flags & STEP_SENSORS) && warp == 0) sensor_taps<T, N>(e, S, M, ws.ax, taps, ntap, lane);
         env_sync<T, N>(ws);
       } else wide_phase_idle<T, N>();
     }
     if (valid && tid == 0) e.wrist_z = (float)ws.ax.wrist_z;
+    if (valid && warp == 0 && ntap > 0) { __syncwarp(); process_taps<T, N>(e, S, M, taps, ntap, lane); }
   }
   if (!valid) return;
+  env_sync<T, N>(ws);
   if ((flags & STEP_TAIL) && tid == 0) {
     sense_gripper_state<T>(e, S, M);
     update_env<T>(e, S, ws.ax);
@@ -338,7 +359,7 @@ int launch_step_wide_TN(GmjHandle* h, int flags, int nsub, const int32_t* action
   const int blocks = (h->n_envs + EPB - 1) / EPB;
   const int list_blocks = combined ? blocks : 0;        // worst case every env owes a lift; empty list blocks exit at once
   k_step_wide<T, N><<<blocks + list_blocks, GMJ_WNT * EPB, smem, st>>>((EnvState<T, GMJ_WQC>*)h->envs, (const DevModel<T, GMJ_WNT>*)h->model, h->settings,
-      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks, h->perm, h->hist);
+      h->n_envs, flags, nsub, actions, frac, obs, reward, done, events, h->err_flag, h->env_list, h->env_count, list_blocks, h->perm, h->hist, (T*)h->taps);
   CK(cudaGetLastError());
   h->smem_bytes = smem;
   return 0;

@@ -187,13 +187,12 @@ template <typename T, int QC> __device__ inline int ready_to_read(EnvState<T, QC
 
 // luke::read_armadillo_gauge (src/myfunctions.cpp:2699-2795): cubic least squares through the
 // N+1 joint positions of one finger evaluated at 50 mm, in mm. FP64 (arma::polyfit is double).
-template <typename T, int N, int QC>
-__device__ inline float read_gauge(const EnvState<T, QC>& e, const DevModelS<T>& M, int finger) {
-  double L = (double)M.segment_length;
+template <typename T, int N>
+__device__ inline float read_gauge_q(const T* qf, double L) {          // qf: the N segment joint angles of one finger
   double X[N + 1][4], y[N + 1], fx[N + 1];
   double cum = 0; fx[0] = 0; y[0] = 0;
   for (int i = 0; i < N; i++) {
-    cum += (double)e.qpos[3 + finger * (N + 2) + i];
+    cum += (double)qf[i];
     fx[i + 1] = fx[i] + L * nd_cos(cum);
     y[i + 1] = y[i] + L * nd_sin(cum);
   }
@@ -234,6 +233,10 @@ __device__ inline float read_gauge(const EnvState<T, QC>& e, const DevModelS<T>&
   yv = (float)(yv + coeff[2] * xp);
   yv = (float)(yv + coeff[3] * 1.0);
   return yv * 1000;
+}
+template <typename T, int N, int QC>
+__device__ inline float read_gauge(const EnvState<T, QC>& e, const DevModelS<T>& M, int finger) {
+  return read_gauge_q<T, N>(&e.qpos[3 + finger * (N + 2)], (double)M.segment_length);
 }
 
 // ObjectHandler::extract_forces_faster (src/objecthandler.cpp:737-992) with geom classes
@@ -280,54 +283,105 @@ __device__ inline void extract_forces(const EnvState<T, QC>& e, const WarpAux<T>
   }
 }
 
-// MjClass::monitor_sensors (src/mjclass.cpp:741-898)
+// MjClass::monitor_sensors (src/mjclass.cpp:741-898), split in two.
+//  sensor_taps()   -- every substep, warp-parallel and cheap: the four 10 Hz timers (lanes 0-3, Sensor::ready_to_read)
+//                     and, when one fires, a RECORD of the raw inputs of that tap (segment joint angles, finger-axial
+//                     and palm force sums, wrist force) appended to the env's tap buffer in HBM.
+//  process_taps()  -- after the substep loop: the records in time order through the reference's per-tap pipeline
+//                     (cubic gauge fit in FP64, SI copy, normalisation, noise draws, window adds), so results and RNG
+//                     draw order are exactly those of doing it inside the loop.
+// Why: the FP64 fits + noise (libm log / cos) cost ~60 k cycles on three lanes; inside the lockstep loop every warp of
+// the block waited for whichever env had a tap that substep (r2 per-env cycle counters: 6.3 k cycles of tail work and
+// ~11 k cycles of waiting per substep).
+#define GMJ_MAXTAP 8
+#define GMJ_TAP_HDR 6                 // mask, wrist, palm, axial[3]; then 3 N joint angles
 template <typename T, int N, int QC>
-__device__ inline void monitor_sensors(EnvState<T, QC>& e, const DevSettings& S, const DevModelS<T>& M, const WarpAux<T>& ax, int lane) {
-  // warp-collective: lane 0 owns the sensor state, the three cubic gauge fits (FP64 QR) run on lanes 0-2
+__device__ inline void process_taps(EnvState<T, QC>& e, const DevSettings& S, const DevModelS<T>& M, const T* taps, int ntap, int lane) {
   const double* g = S.s.general;
+  constexpr int STRIDE = GMJ_TAP_HDR + 3 * N;
+  for (int r = 0; r < ntap; r++) {
+    const T* rec = taps + (size_t)r * STRIDE;
+    const int mask = (int)rec[0];
+    float gfit = 0.0f;
+    if ((mask & 1) && lane < 3) gfit = read_gauge_q<T, N>(rec + GMJ_TAP_HDR + lane * N, (double)M.segment_length);
+    const float gfit0 = __shfl_sync(GMJ_FULL, gfit, 0), gfit1 = __shfl_sync(GMJ_FULL, gfit, 1), gfit2 = __shfl_sync(GMJ_FULL, gfit, 2);
+    if (lane != 0) continue;
+    if (mask & 1) {
+      for (int f = 0; f < 3; f++) {
+        float gv = f == 0 ? gfit0 : (f == 1 ? gfit1 : gfit2);
+        e.si_latest[f] = (float)((double)gv * g[GS_sim_gauge_raw_to_N_factor]);   // gfloat * double member (src/mjclass.cpp:755-757)
+        gv = apply_normalisation(S.s.sensor[GSEN_bending_gauge], gv);
+        gv = apply_noise(e, S, GSEN_bending_gauge, gv, f + 1);
+        win_add(e, ST_gauge + f, gv);
+      }
+    }
+    if (mask & 2) {
+      for (int f = 0; f < 3; f++) {
+        float av = (float)rec[3 + f];
+        av = apply_normalisation(S.s.sensor[GSEN_axial_gauge], av);
+        av = apply_noise(e, S, GSEN_axial_gauge, av, f + 1);
+        win_add(e, ST_axial + f, av);
+      }
+    }
+    if (mask & 4) {
+      float pv = (float)rec[2];
+      pv = (float)(pv * g[GS_palm_scale_factor]);
+      e.si_latest[3] = pv;
+      pv = apply_normalisation(S.s.sensor[GSEN_palm], pv);
+      pv = apply_noise(e, S, GSEN_palm, pv, 1);
+      win_add(e, ST_palm, pv);
+    }
+    if (mask & 8) {
+      float z = (float)rec[1];
+      z -= (float)S.s.sensor[GSEN_wrist_Z][GSF_raw_value_offset];
+      e.si_latest[4] = z;
+      z = apply_normalisation(S.s.sensor[GSEN_wrist_Z], z);
+      z = apply_noise(e, S, GSEN_wrist_Z, z, 1);
+      win_add(e, ST_wristz, z);
+    }
+  }
+  __syncwarp();
+}
+// ntap: records already in the buffer (kept by the caller, uniform over the warp). A full buffer is processed on the
+// spot (settings with a very high read rate), so any setting gives the reference's results.
+template <typename T, int N, int QC>
+__device__ __forceinline__ void sensor_taps(EnvState<T, QC>& e, const DevSettings& S, const DevModelS<T>& M, const WarpAux<T>& ax,
+                                            T* taps, int& ntap, int lane) {
   int due = 0;
-  if (lane == 0) due = ready_to_read(e, S, GSEN_bending_gauge, 0);
-  due = __shfl_sync(GMJ_FULL, due, 0);
-  float gfit = 0.0f;
-  if (due && lane < 3) gfit = read_gauge<T, N>(e, M, lane);
-  const float gfit0 = __shfl_sync(GMJ_FULL, gfit, 0), gfit1 = __shfl_sync(GMJ_FULL, gfit, 1), gfit2 = __shfl_sync(GMJ_FULL, gfit, 2);
-  if (lane != 0) return;
-  bool got = false; DevForces F;
-  if (due) {
-    for (int f = 0; f < 3; f++) {
-      float gv = f == 0 ? gfit0 : (f == 1 ? gfit1 : gfit2);
-      e.si_latest[f] = (float)((double)gv * g[GS_sim_gauge_raw_to_N_factor]);   // gfloat * double member (src/mjclass.cpp:755-757)
-      gv = apply_normalisation(S.s.sensor[GSEN_bending_gauge], gv);
-      gv = apply_noise(e, S, GSEN_bending_gauge, gv, f + 1);
-      win_add(e, ST_gauge + f, gv);
+  if (lane < 4) {
+    const int sen = lane == 0 ? GSEN_bending_gauge : (lane == 1 ? GSEN_axial_gauge : (lane == 2 ? GSEN_palm : GSEN_wrist_Z));
+    if (e.time > e.last_read_time[lane] + S.read_between[sen]) { e.last_read_time[lane] = e.time; due = 1; }   // src/mjclass.h:225-241
+  }
+  const unsigned m = __ballot_sync(GMJ_FULL, due) & 0xfu;
+  if (!m) return;
+  if (ntap == GMJ_MAXTAP) { __syncwarp(); process_taps<T, N>(e, S, M, taps, ntap, lane); ntap = 0; }
+  constexpr int STRIDE = GMJ_TAP_HDR + 3 * N;
+  T* rec = taps + (size_t)ntap * STRIDE;
+  if (m & 1) for (int i = lane; i < 3 * N; i += 32) { const int f = i / N; rec[GMJ_TAP_HDR + i] = e.qpos[3 + f * (N + 2) + (i - f * N)]; }
+  T ax3[3] = { 0, 0, 0 }, palm = 0;
+  if ((m & 6) && e.has_object) {
+    // ObjectHandler::extract_forces_faster restricted to what the taps read: local x of the force sums on each finger
+    // and on the palm over ALL contacts (src/objecthandler.cpp:737-992); lane c takes contact c
+    T gx = 0, gy = 0, gz = 0; int ca = 0, cb = 0;
+    if (lane < ax.ncon) {
+      const DevContact<T>& cn = ax.con[lane];
+      ca = cn.cls1; cb = cn.cls2;
+#pragma unroll
+      for (int k = 0; k < 3; k++) { gx += cn.force[k] * cn.frame[3 * k]; gy += cn.force[k] * cn.frame[3 * k + 1]; gz += cn.force[k] * cn.frame[3 * k + 2]; }
+    }
+#pragma unroll
+    for (int f = 0; f < 4; f++) {
+      const int cls = f < 3 ? GMJ_CLS_F1 + f : GMJ_CLS_PALM;
+      const bool w = (ca == cls || cb == cls);
+      const T* R = f < 3 ? ax.fingerR[f] : ax.palmR;
+      // local x component: column 0 of the body's rotation matrix dotted with the world force
+      const T v = warp_sum(w ? (R[0] * gx + R[3] * gy + R[6] * gz) : T(0));
+      if (f < 3) ax3[f] = v; else palm = v;
     }
   }
-  if (ready_to_read(e, S, GSEN_axial_gauge, 1)) {
-    if (!got) { extract_forces(e, ax, F); got = true; }
-    for (int f = 0; f < 3; f++) {
-      float av = (float)F.all_f_loc[f][0];
-      av = apply_normalisation(S.s.sensor[GSEN_axial_gauge], av);
-      av = apply_noise(e, S, GSEN_axial_gauge, av, f + 1);
-      win_add(e, ST_axial + f, av);
-    }
-  }
-  if (ready_to_read(e, S, GSEN_palm, 2)) {
-    if (!got) { extract_forces(e, ax, F); got = true; }
-    float pv = (float)F.all_palm_loc[0];
-    pv = (float)(pv * g[GS_palm_scale_factor]);
-    e.si_latest[3] = pv;
-    pv = apply_normalisation(S.s.sensor[GSEN_palm], pv);
-    pv = apply_noise(e, S, GSEN_palm, pv, 1);
-    win_add(e, ST_palm, pv);
-  }
-  if (ready_to_read(e, S, GSEN_wrist_Z, 3)) {
-    float z = (float)ax.wrist_z;
-    z -= (float)S.s.sensor[GSEN_wrist_Z][GSF_raw_value_offset];
-    e.si_latest[4] = z;
-    z = apply_normalisation(S.s.sensor[GSEN_wrist_Z], z);
-    z = apply_noise(e, S, GSEN_wrist_Z, z, 1);
-    win_add(e, ST_wristz, z);
-  }
+  if (lane == 0) { rec[0] = (T)(int)m; rec[1] = ax.wrist_z; rec[2] = palm; rec[3] = ax3[0]; rec[4] = ax3[1]; rec[5] = ax3[2]; }
+  ntap++;
+  __syncwarp();
 }
 
 // ------------------------------------------------------------------ stepper + welds

@@ -420,6 +420,8 @@ __device__ __forceinline__ int lcp_solve(WarpShared<T, N, QC>& ws, int nr, int l
                  : lcp_solve_impl<T, N, QC, false>(ws, nr, lane, b, R, type, f, warm);
 }
 
+#include "gmj_primal.cuh"
+
 // ------------------------------------------------------------------ block lockstep
 // The substep is ~10 k straight-line SASS instructions per warp against a 32 KB L1.5 I-cache, so it
 // runs at the speed of instruction fetch. Phase barriers keep the warps of a block on the same code
@@ -877,7 +879,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
       T Jo[6];
 #pragma unroll
       for (int i = 0; i < 6; i++) Jo[i] = Joc[0][i] + sg2 * Joc[t][i];
-      put_row<T, N>(ws, tp, rsqo, nr + k, xw[0] + sg2 * xw[t], Jo, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr, -1);
+      put_row<T, N>(ws, tp, rsqo, nr + k, xw[0] + sg2 * xw[t], Jo, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr, gripper_part ? -1 : -2);
     }
     nr += 4;
   }
@@ -894,14 +896,31 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   GMJ_PHASE(6);
   // lane owns rows r0 = lane and r1 = lane + 32
   const int r0 = lane, r1 = lane + 32;
+  int iters = 0;
+  T g = 0, go = 0;
+  const T tc = maxT<T>(M.solref_tc, 2 * dt), dr = M.solref_dr, dmax = M.solimp[1];
+  const T kk = rcpT<T>(dmax * dmax * tc * tc * dr * dr), bb = T(2) * rcpT<T>(dmax * tc);
+#ifndef GMJ_DUAL
+  // ------------------------------------------------------------------ primal active-set solve (gmj_primal.cuh)
+  {
+    T pf[2] = { 0, 0 };
+    GMJ_PHASE(7);
+    if (nr > 0) iters = primal_solve<T, N>(ws, tp, M.solimp, kk, bb, nr, lane, e.nrow_prev == nr, e.fprev, pf, g, go);
+    __syncwarp();
+    if (r0 < nr) e.fprev[r0] = pf[0];
+    if (r1 < nr) e.fprev[r1] = pf[1];
+    if (lane == 0) { e.nrow_prev = nr; ws.ax.niter = iters; }
+    __syncwarp();
+    GMJ_PHASE(8);
+    // g = whitened constraint force = x - x_s straight from the primal solution (sum_r W[r] f_r of the dual path)
+  }
+#else
   T bcol[2];
   form_A<T, N>(ws, nr, lane, bcol);
   __syncwarp();
   // regulariser, reference acceleration, PGS state per owned row
   T pf[2], py[2], pb[2], pR[2], pinv[2]; int ptype[2];
   {
-    T tc = maxT<T>(M.solref_tc, 2 * dt), dr = M.solref_dr, dmax = M.solimp[1];
-    T kk = rcpT<T>(dmax * dmax * tc * tc * dr * dr), bb = T(2) * rcpT<T>(dmax * tc);
 #pragma unroll
     for (int slot = 0; slot < 2; slot++) {
       int r = slot ? r1 : r0;
@@ -930,7 +949,6 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   // the solution is unique: the oracle reaches it with PGS converged to 1e-13, here it is found by
   // block principal pivoting over the active set (warm-started from the previous substep) with an
   // in-place warp Cholesky per pivot -- a few thousand cycles instead of hundreds of GS sweeps.
-  int iters = 0;
   if (nr > 0) iters = lcp_solve<T, N>(ws, nr, lane, pb, pR, ptype, pf, e.nrow_prev == nr);
   if (r0 < nr) e.fprev[r0] = pf[0];
   if (r1 < nr) e.fprev[r1] = pf[1];
@@ -939,12 +957,12 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
 
   // ------------------------------------------------------------------ constraint force, integration
   GMJ_PHASE(8);
-  T g = 0, go = 0;
   for (int r = 0; r < nr; r++) {
     T fr = e.fprev[r];
     if (tp.act) g += ws.W[r][lane] * fr;
     if (lane < 6) go += ws.W[r][B + lane] * fr;
   }
+#endif
   // tau_c = L D^1/2 g
   T tauc = ldl_mulL<T, N>(tp, Mrow, lb, tp.act ? g * sqrtT<T>(D) : T(0));
   // limit-row forces acting on the base joint enter the wrist force sensor

@@ -1,0 +1,302 @@
+// gmj_primal.cuh -- constraint solve of the lane-per-dof kernel in PRIMAL (acceleration) space.
+//
+// The soft-constraint problem of one substep is, in whitened coordinates x = D^1/2 L^T qacc (M = L D L^T),
+//     minimise  1/2 |x - x_s|^2  +  sum_{r active}  (w_r . x - aref_r)^2 / (2 R_r)
+// with w_r the whitened constraint rows (ws.W), x_s the whitened smooth force (row nr of ws.W), R_r MuJoCo's
+// regulariser; row r is active when it is an equality or its force f_r = -(w_r . x - aref_r) / R_r is positive.
+// Round 1 solved the DUAL of this, (A + R) f + b = w with A = W W^T, by block principal pivoting with a dense warp
+// Cholesky of the active rows: the r2 per-env cycle counters put W W^T + the factorisation at 34 % of a substep on
+// average (17 rows) and at 100 k of 180 k cycles for the envs that hold a lockstep block back (46 rows) -- dense work
+// that grows with the square / cube of the row count.
+// The primal normal matrix  H = I + sum_active w_r w_r^T / R_r  has the sparsity of the mass matrix instead: a whitened
+// row touches one finger chain (or the palm), the base and the object, never two fingers. So H is block-arrow --
+// three dense (N + 2)^2 finger blocks + the palm, each coupled only to the 7 root coordinates (base + object 6) -- and
+// its factorisation is the tree LDL^T the kernel already runs for M, whatever the number of rows: leaves in registers
+// (lane = row, pivot rows by shuffle) with the 7 coupling columns and the right-hand side riding along, then a 7 x 7
+// Schur complement solved redundantly by every lane. Rows only enter through the rank-one accumulation of H, which is
+// linear in the row count. The pivoting rule (flip every violated row, Murty's least-index rule after three
+// non-improving rounds), tolerances and warm start are those of the dual solver; the solution is the same unique one.
+#pragma once
+
+// scratch laid over the packed-A storage of WarpShared (unused in primal mode)
+template <typename T, int N> struct PrimalScratch {
+  static constexpr int NL = N + 2, B = 3 * N + 8;
+  T Lc[3][NL][NL + 1];      // finger blocks of the factor, for the column walk of the back substitution
+  T hc[B][8];               // per leaf: coupling row scaled by D^-1/2 (7) and y D^-1/2
+  T root[36];               // Schur complement: 28 packed entries + 7 right-hand sides
+  T x[WarpShared<T, N>::NW + 3];   // solution (whitened acceleration)
+};
+
+// H x = g for the current active set. act0/act1: this lane's rows lane, lane + 32 active. Returns x in sc.x and this
+// lane's entry in xl (gripper coordinate `lane`), xr[7] the root solution (base, object 0-5), replicated.
+template <typename T, int N>
+__device__ __forceinline__ void primal_factor_solve(WarpShared<T, N>& ws, PrimalScratch<T, N>& sc, const Topo<N>& tp, int nr, int lane,
+                                                     unsigned m0, unsigned m1, T& xl, T (&xr)[7]) {
+  constexpr int NL = N + 2, B = 3 * N + 8, PALM = 3 * N + 7;
+  const bool leaf = tp.act && lane != 0;
+  // root entry owned by this lane: e = m (m + 1) / 2 + n, m >= n
+  int em = 0, en = 0;
+  { int e = lane < 28 ? lane : 0; while ((em + 1) * (em + 2) / 2 <= e) em++; en = e - em * (em + 1) / 2; }
+  const int cm = em == 0 ? 0 : B + em - 1, cn = en == 0 ? 0 : B + en - 1;      // W columns of the two root coordinates
+  const T* xs = ws.W[nr];
+  T Hrow[NL], Hc[7], gl = tp.act ? xs[lane] : T(0);
+#pragma unroll
+  for (int k = 0; k < NL; k++) Hrow[k] = (k == tp.local && leaf) ? T(1) : T(0);
+#pragma unroll
+  for (int m = 0; m < 7; m++) Hc[m] = 0;
+  T Se = (lane < 28 && em == en) ? T(1) : T(0);
+  T gr = (lane < 28 && em == en) ? xs[cm] : T(0);
+  // ---- H and g: one rank-one term per active row
+#pragma unroll 1
+  for (int r = 0; r < nr; r++) {
+    if (!(((r < 32 ? m0 >> r : m1 >> (r - 32))) & 1)) continue;
+    const T* wr = ws.W[r];
+    const T s = ws.rjv[r], sa = s * ws.rpos[r];          // 1 / R_r and aref_r / R_r (primal_prepare)
+    T wroot[7];
+    wroot[0] = wr[0];
+#pragma unroll
+    for (int m = 1; m < 7; m++) wroot[m] = wr[B + m - 1];
+    if (ws.rlane[r] != -2) {                              // the row has a gripper part (anything but object-ground / base-only)
+      const T wc = leaf ? wr[lane] : T(0);
+      const T swc = s * wc;
+#pragma unroll
+      for (int k = 0; k < NL; k++) if (k <= tp.local) Hrow[k] += swc * wr[tp.fb + k];
+#pragma unroll
+      for (int m = 0; m < 7; m++) Hc[m] += swc * wroot[m];
+      gl += sa * wc;
+    }
+    // root block
+    {
+      const T a = em == 0 ? wroot[0] : wr[cm], b = en == 0 ? wroot[0] : wr[cn];
+      if (lane < 28) { Se += s * a * b; if (em == en) gr += sa * a; }
+    }
+  }
+  // ---- leaves: LDL^T inside each finger chain (pivot row by shuffle), couplings and right-hand side ride along
+#pragma unroll
+  for (int k = 0; k < NL - 1; k++) {
+    const int p = tp.fb + k;
+    const T Dk = __shfl_sync(GMJ_FULL, Hrow[k], p);
+    const T inv = rcpT<T>(tp.chain ? Dk : T(1));
+    const bool below = tp.chain && tp.local > k;
+    const T hk = Hrow[k];
+    const T l = below ? hk * inv : T(0);
+#pragma unroll
+    for (int j = k + 1; j < NL; j++) {
+      const T hjk = __shfl_sync(GMJ_FULL, hk, tp.fb + j);
+      if (below && tp.local >= j) Hrow[j] -= l * hjk;
+    }
+#pragma unroll
+    for (int m = 0; m < 7; m++) { const T cp = __shfl_sync(GMJ_FULL, Hc[m], p); if (below) Hc[m] -= l * cp; }
+    { const T gp = __shfl_sync(GMJ_FULL, gl, p); if (below) gl -= l * gp; }
+    if (below) Hrow[k] = l;
+  }
+  T D = T(1);
+#pragma unroll
+  for (int k = 0; k < NL; k++) if (tp.local == k) D = Hrow[k];
+  if (!leaf) D = T(1);
+  const T dinv = rcpT<T>(D), dis = sqrtT<T>(dinv);
+  // factor columns + scaled couplings to shared memory
+  if (tp.chain) { const int fi = (lane - 1) / NL;
+#pragma unroll
+    for (int k = 0; k < NL; k++) sc.Lc[fi][tp.local][k] = (k < tp.local) ? Hrow[k] : T(0); }
+  if (tp.act) {
+#pragma unroll
+    for (int m = 0; m < 7; m++) sc.hc[lane][m] = leaf ? Hc[m] * dis : T(0);
+    sc.hc[lane][7] = leaf ? gl * dis : T(0);
+  }
+  __syncwarp();
+  // ---- Schur complement on the root: S -= sum_leaves u u^T, g_root -= sum_leaves u y'
+  if (lane < 28) {
+    T a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+#pragma unroll 2
+    for (int c = 1; c + 1 < B; c += 2) {
+      a0 += sc.hc[c][em] * sc.hc[c][en]; a1 += sc.hc[c + 1][em] * sc.hc[c + 1][en];
+      b0 += sc.hc[c][em] * sc.hc[c][7]; b1 += sc.hc[c + 1][em] * sc.hc[c + 1][7];
+    }
+    if (!(B & 1)) { a0 += sc.hc[B - 1][em] * sc.hc[B - 1][en]; b0 += sc.hc[B - 1][em] * sc.hc[B - 1][7]; }
+    Se -= a0 + a1;
+    sc.root[lane] = Se;
+    if (em == en) sc.root[28 + em] = gr - (b0 + b1);
+  }
+  __syncwarp();
+  // ---- 7 x 7 Cholesky + solve, every lane redundantly (uniform straight-line code on broadcast loads)
+  {
+    T Sm[28];
+#pragma unroll
+    for (int i = 0; i < 28; i++) Sm[i] = sc.root[i];
+#pragma unroll
+    for (int m = 0; m < 7; m++) xr[m] = sc.root[28 + m];
+#pragma unroll
+    for (int j = 0; j < 7; j++) {
+      T d = Sm[j * (j + 1) / 2 + j];
+#pragma unroll
+      for (int k = 0; k < j; k++) d -= Sm[j * (j + 1) / 2 + k] * Sm[j * (j + 1) / 2 + k];
+      const T inv = rsqrtT<T>(maxT<T>(d, T(1e-30)));
+      Sm[j * (j + 1) / 2 + j] = inv;                       // 1 / L_jj
+#pragma unroll
+      for (int i = j + 1; i < 7; i++) {
+        T v = Sm[i * (i + 1) / 2 + j];
+#pragma unroll
+        for (int k = 0; k < j; k++) v -= Sm[i * (i + 1) / 2 + k] * Sm[j * (j + 1) / 2 + k];
+        Sm[i * (i + 1) / 2 + j] = v * inv;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 7; i++) {
+#pragma unroll
+      for (int k = 0; k < i; k++) xr[i] -= Sm[i * (i + 1) / 2 + k] * xr[k];
+      xr[i] *= Sm[i * (i + 1) / 2 + i];
+    }
+#pragma unroll
+    for (int i = 6; i >= 0; i--) {
+#pragma unroll
+      for (int k = i + 1; k < 7; k++) xr[i] -= Sm[k * (k + 1) / 2 + i] * xr[k];
+      xr[i] *= Sm[i * (i + 1) / 2 + i];
+    }
+  }
+  // ---- leaves back: x_c = (y_c - Hc_c . x_root) / D_c - sum_{below} L[i][c] x_i
+  T x = gl;
+#pragma unroll
+  for (int m = 0; m < 7; m++) x -= Hc[m] * xr[m];
+  x = leaf ? x * dinv : T(0);
+  {
+    const int fi = tp.chain ? (lane - 1) / NL : 0;
+#pragma unroll
+    for (int k = NL - 1; k >= 1; k--) {
+      const T xk = __shfl_sync(GMJ_FULL, x, tp.fb + k);
+      if (tp.chain && tp.local < k) x -= sc.Lc[fi][k][tp.local] * xk;
+    }
+  }
+  if (lane == 0) x = xr[0];
+  xl = x;
+  if (tp.act) sc.x[lane] = x;
+  if (lane < 6) sc.x[B + lane] = xr[1 + lane];
+  __syncwarp();
+}
+
+// Per row (lane = row, rows lane and lane + 32): reference acceleration, regulariser from the row norms
+// (A_rr = |w_r|^2; contacts use the norm of the whitened NORMAL row, the mean of their first two pyramid rows),
+// unconstrained residual for the cold start. Leaves aref in ws.rpos and 1 / R in ws.rjv.
+template <typename T, int N>
+__device__ __forceinline__ void primal_prepare(WarpShared<T, N>& ws, const T* solimp, T kk, T bb, int nr, int lane, bool warm,
+                                               const T* fprev, bool (&act)[2], int (&type)[2], T (&Rr)[2], T (&aref)[2]) {
+  constexpr int NW = WarpShared<T, N>::NW;
+#pragma unroll
+  for (int slot = 0; slot < 2; slot++) {
+    const int r = lane + 32 * slot;
+    act[slot] = false; type[slot] = ROW_EQ; Rr[slot] = 1; aref[slot] = 0;
+    if (slot == 1 && nr <= 32) break;
+    if (r < nr) {
+      const T pos = ws.rpos[r];
+      const T imp = impedance<T>(solimp, pos);
+      const T ar = -bb * ws.rjv[r] - kk * imp * pos;
+      const int ty = ws.rtype[r];
+      const T* wr = ws.W[r];
+      const T* xs = ws.W[nr];
+      T n0 = 0, n1 = 0, j0 = 0, j1 = 0;
+      if (ty == ROW_CONTACT) {
+        const int rf = ws.rfirst[r];
+        const T* wa = ws.W[rf]; const T* wb = ws.W[rf + 1];
+#pragma unroll
+        for (int c = 0; c + 1 < NW; c += 2) {
+          const T u0 = wa[c] + wb[c], u1 = wa[c + 1] + wb[c + 1];
+          n0 += u0 * u0; n1 += u1 * u1;
+          if (!warm) { j0 += wr[c] * xs[c]; j1 += wr[c + 1] * xs[c + 1]; }
+        }
+        if (NW & 1) { const T u0 = wa[NW - 1] + wb[NW - 1]; n0 += u0 * u0; if (!warm) j0 += wr[NW - 1] * xs[NW - 1]; }
+        const T mu = ws.rmu[r];
+        const T Ann = T(0.25) * (n0 + n1);
+        Rr[slot] = 2 * mu * mu * (1 - imp) * rcpT<T>(imp) * (1 + mu * mu) * Ann;
+      } else {
+#pragma unroll
+        for (int c = 0; c + 1 < NW; c += 2) {
+          n0 += wr[c] * wr[c]; n1 += wr[c + 1] * wr[c + 1];
+          if (!warm) { j0 += wr[c] * xs[c]; j1 += wr[c + 1] * xs[c + 1]; }
+        }
+        if (NW & 1) { n0 += wr[NW - 1] * wr[NW - 1]; if (!warm) j0 += wr[NW - 1] * xs[NW - 1]; }
+        Rr[slot] = (1 - imp) * rcpT<T>(imp) * (n0 + n1);
+      }
+      Rr[slot] = maxT<T>(Rr[slot], T(1e-15));
+      aref[slot] = ar; type[slot] = ty;
+      act[slot] = ty == ROW_EQ || (warm ? fprev[r] > 0 : (j0 + j1) - ar < 0);
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int slot = 0; slot < 2; slot++) {
+    const int r = lane + 32 * slot;
+    if (r < nr) { ws.rpos[r] = aref[slot]; ws.rjv[r] = rcpT<T>(Rr[slot]); }
+  }
+  __syncwarp();
+}
+
+// The whole solve. Out: force of this lane's rows in f[2], x - x_s of this lane's gripper coordinate in dx and of the
+// object coordinates in dxo (lanes 0-5). Returns the number of pivoting rounds.
+template <typename T, int N>
+__device__ int primal_solve(WarpShared<T, N>& ws, const Topo<N>& tp, const T* solimp, T kk, T bb, int nr, int lane, bool warm,
+                            const T* fprev, T (&f)[2], T& dx, T& dxo) {
+  constexpr int NW = WarpShared<T, N>::NW, B = 3 * N + 8;
+  static_assert(sizeof(PrimalScratch<T, N>) <= sizeof(ws.A), "primal scratch must fit the packed-A storage");
+  PrimalScratch<T, N>& sc = *reinterpret_cast<PrimalScratch<T, N>*>(ws.A);
+  const T eps = sizeof(T) == 8 ? T(1e-12) : T(2e-6);
+  const int maxit = 40;
+  bool act[2]; int type[2]; T Rr[2], aref[2];
+  primal_prepare<T, N>(ws, solimp, kk, bb, nr, lane, warm, fprev, act, type, Rr, aref);
+  const int r0 = lane, r1 = lane + 32;
+  const bool two = nr > 32;
+  const T* xs = ws.W[nr];
+  // scale of the right-hand side for the slack tolerance (the dual solver's |b| = |w_r . x_s - aref_r|): aref dominates
+  const T bscale = warp_max(maxT<T>(r0 < nr ? absT<T>(aref[0]) : T(0), (two && r1 < nr) ? absT<T>(aref[1]) : T(0)));
+  int best = 1 << 30, patience = 3, it = 0;
+  T xl = 0, xr[7];
+  T f0 = 0, f1 = 0;
+  for (;; ) {
+    it++;
+    const unsigned m0 = __ballot_sync(GMJ_FULL, act[0]), m1 = __ballot_sync(GMJ_FULL, act[1]);
+    primal_factor_solve<T, N>(ws, sc, tp, nr, lane, m0, m1, xl, xr);
+    // ---- residuals jar_r = w_r . x - aref_r; force of an active row -jar / R, slack of an inactive row jar
+    T j0 = 0, j1 = 0;
+    if (r0 < nr) {
+      const T* wr = ws.W[r0];
+      T a0 = 0, a1 = 0;
+#pragma unroll
+      for (int c = 0; c + 1 < NW; c += 2) { a0 += wr[c] * sc.x[c]; a1 += wr[c + 1] * sc.x[c + 1]; }
+      if (NW & 1) a0 += wr[NW - 1] * sc.x[NW - 1];
+      j0 = (a0 + a1) - aref[0];
+    }
+    if (two && r1 < nr) {
+      const T* wr = ws.W[r1];
+      T a0 = 0, a1 = 0;
+#pragma unroll
+      for (int c = 0; c + 1 < NW; c += 2) { a0 += wr[c] * sc.x[c]; a1 += wr[c + 1] * sc.x[c + 1]; }
+      if (NW & 1) a0 += wr[NW - 1] * sc.x[NW - 1];
+      j1 = (a0 + a1) - aref[1];
+    }
+    f0 = act[0] ? -j0 * rcpT<T>(Rr[0]) : T(0); f1 = act[1] ? -j1 * rcpT<T>(Rr[1]) : T(0);
+    const T fscale = warp_max(maxT<T>(absT<T>(f0), absT<T>(f1)));
+    T epsr = eps;
+    for (int k = GMJ_LCP_GROW_FROM; k < it && epsr < T(1e-2); k++) epsr *= GMJ_LCP_GROW;
+    const T tolf = epsr * (1 + fscale), tolw = epsr * (1 + bscale);
+    const bool bad0 = r0 < nr && type[0] != ROW_EQ && (act[0] ? f0 < -tolf : j0 < -tolw);
+    const bool bad1 = two && r1 < nr && type[1] != ROW_EQ && (act[1] ? f1 < -tolf : j1 < -tolw);
+    const unsigned b0 = __ballot_sync(GMJ_FULL, bad0), b1 = __ballot_sync(GMJ_FULL, bad1);
+    const int ninf = __popc(b0) + __popc(b1);
+    if (ninf == 0 || it >= maxit) break;
+    bool block = true;
+    if (ninf < best) { best = ninf; patience = 3; }
+    else if (patience > 0) patience--;
+    else block = false;
+    if (block) { if (bad0) act[0] = !act[0]; if (bad1) act[1] = !act[1]; }
+    else {                                     // Murty: flip only the infeasible row of largest index
+      const int top = b1 ? 32 + (31 - __clz(b1)) : (31 - __clz(b0));
+      if (r0 == top) act[0] = !act[0];
+      if (r1 == top) act[1] = !act[1];
+    }
+    __syncwarp();
+  }
+  f[0] = (type[0] != ROW_EQ && f0 < 0) ? T(0) : f0;
+  f[1] = (type[1] != ROW_EQ && f1 < 0) ? T(0) : f1;
+  dx = tp.act ? xl - xs[lane] : T(0);
+  dxo = lane < 6 ? xr[1 + lane] - xs[B + lane] : T(0);
+  return it;
+}

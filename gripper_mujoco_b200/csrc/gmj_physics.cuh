@@ -24,7 +24,14 @@ struct WarpShared {
   EnvState<T, QC> e;
   WarpAux<T> ax;
   T W[GMJ_RMAX + 1][WS];            // whitened rows; row nrow holds the whitened smooth force
-  T A[GMJ_RMAX * (GMJ_RMAX + 1) / 2]; // packed lower triangle of W W^T, overwritten by its Cholesky factor
+  // dual solve (wide kernels, -DGMJ_DUAL): packed lower triangle of W W^T, overwritten by its Cholesky factor;
+  // primal solve (lane-per-dof kernels): only the PrimalScratch of gmj_primal.cuh lives here
+#ifdef GMJ_DUAL
+  static constexpr int ASZ = GMJ_RMAX * (GMJ_RMAX + 1) / 2;
+#else
+  static constexpr int ASZ = QC == 40 ? 3 * (N + 2) * (N + 3) + 8 * B + 36 + NW + 3 : GMJ_RMAX * (GMJ_RMAX + 1) / 2;
+#endif
+  T A[ASZ];
   T u[WS + 1];                      // W^T f scratch of the LCP solver
   T L2[3][N + 2][N + 3];            // second factor, for column access in the back substitution
   T qfk[QC];                        // qpos of the last kinematics pass (weld anchors)

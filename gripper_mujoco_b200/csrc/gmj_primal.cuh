@@ -32,7 +32,7 @@ template <typename T, int N> struct PrimalScratch {
 template <typename T, int N>
 __device__ __forceinline__ void primal_factor_solve(WarpShared<T, N>& ws, PrimalScratch<T, N>& sc, const Topo<N>& tp, int nr, int lane,
                                                      unsigned m0, unsigned m1, T& xl, T (&xr)[7]) {
-  constexpr int NL = N + 2, B = 3 * N + 8, PALM = 3 * N + 7;
+  constexpr int NL = N + 2, B = 3 * N + 8;
   const bool leaf = tp.act && lane != 0;
   // root entry owned by this lane: e = m (m + 1) / 2 + n, m >= n
   int em = 0, en = 0;

@@ -198,28 +198,20 @@ template <typename T> __device__ __forceinline__ T impedance(const T* solimp, T 
 }
 
 // ---------------------------------------------------------------------------------------------
-// emit one constraint row: whiten the lane-distributed gripper part, store row + meta
-template <typename T, int N>
-__device__ __forceinline__ void emit_row(WarpShared<T, N>& ws, const Topo<N>& tp, const T* Lrow, T lb, T rsq,
-                                         const T* rsqo, int r, T Jl, const T* Jo, int type, T pos, T jv, T mu,
-                                         int first, int jl) {
-  T x = ldl_fwd<T, N>(tp, Lrow, lb, Jl) * rsq;
-  if (tp.act) ws.W[r][tp.lane] = x;
-  if (tp.lane == 0) {
-#pragma unroll
-    for (int k = 0; k < 6; k++) ws.W[r][3 * N + 8 + k] = Jo[k] * rsqo[k];
-    ws.rtype[r] = type; ws.rpos[r] = pos; ws.rjv[r] = jv; ws.rmu[r] = mu; ws.rfirst[r] = first; ws.rlane[r] = jl;
-  }
-}
-
-// store an already whitened row (lane value xw) + meta
+// store an already whitened row (lane value xw) + meta. Jo == nullptr: the row has no object part.
+// (Spreading the twelve lane-0 stores over lanes 0-11 was measured 15 % SLOWER: seven divergent paths per row.)
 template <typename T, int N>
 __device__ __forceinline__ void put_row(WarpShared<T, N>& ws, const Topo<N>& tp, const T* rsqo, int r, T xw,
                                         const T* Jo, int type, T pos, T jv, T mu, int first, int jl) {
   if (tp.act) ws.W[r][tp.lane] = xw;
   if (tp.lane == 0) {
+    if (Jo) {
 #pragma unroll
-    for (int k = 0; k < 6; k++) ws.W[r][3 * N + 8 + k] = Jo[k] * rsqo[k];
+      for (int k = 0; k < 6; k++) ws.W[r][3 * N + 8 + k] = Jo[k] * rsqo[k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < 6; k++) ws.W[r][3 * N + 8 + k] = T(0);
+    }
     ws.rtype[r] = type; ws.rpos[r] = pos; ws.rjv[r] = jv; ws.rmu[r] = mu; ws.rfirst[r] = first; ws.rlane[r] = jl;
   }
 }
@@ -769,7 +761,6 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   // ------------------------------------------------------------------ constraint rows
   GMJ_PHASE(5);
   int nr = 0;
-  const T zero6[6] = { 0, 0, 0, 0, 0, 0 };
   // Welds and joint limits act on ONE joint each: every such row is a multiple of L^-1 e_j, so the unit
   // solves are done four joints at a time and the rows are scaled copies.
   // welds: joint `j` locked at its anchor; rows = world components of the joint axis
@@ -805,7 +796,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
         for (int d = 0; d < 3; d++) {
           if (comp[d] * comp[d] < T(1e-10)) continue;
           if (nr >= GMJ_RMAX) break;
-          put_row<T, N>(ws, tp, rsqo, nr, sgn * comp[d] * xw, zero6, ROW_EQ, sgn * rho * comp[d], sgn * comp[d] * qdj, T(0), nr, j);
+          put_row<T, N>(ws, tp, rsqo, nr, sgn * comp[d] * xw, nullptr, ROW_EQ, sgn * rho * comp[d], sgn * comp[d] * qdj, T(0), nr, j);
           nr++;
         }
       }
@@ -831,8 +822,8 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
         if (j < 0) continue;
         T loj = __shfl_sync(GMJ_FULL, lo, j), hij = __shfl_sync(GMJ_FULL, hi, j), qdj = __shfl_sync(GMJ_FULL, qd, j);
         const T xw = x[m] * rsq;
-        if (((mlo >> j) & 1) && nr < GMJ_RMAX) { put_row<T, N>(ws, tp, rsqo, nr, xw, zero6, ROW_LIMIT, loj, qdj, T(1), nr, j); nr++; }
-        if (((mhi >> j) & 1) && nr < GMJ_RMAX) { put_row<T, N>(ws, tp, rsqo, nr, -xw, zero6, ROW_LIMIT, hij, -qdj, T(-1), nr, j); nr++; }
+        if (((mlo >> j) & 1) && nr < GMJ_RMAX) { put_row<T, N>(ws, tp, rsqo, nr, xw, nullptr, ROW_LIMIT, loj, qdj, T(1), nr, j); nr++; }
+        if (((mhi >> j) & 1) && nr < GMJ_RMAX) { put_row<T, N>(ws, tp, rsqo, nr, -xw, nullptr, ROW_LIMIT, hij, -qdj, T(-1), nr, j); nr++; }
       }
     }
   }
@@ -886,7 +877,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
       T Jo[6];
 #pragma unroll
       for (int i = 0; i < 6; i++) Jo[i] = Joc[0][i] + sg2 * Joc[t][i];
-      put_row<T, N>(ws, tp, rsqo, nr + k, xw[0] + sg2 * xw[t], Jo, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr, gripper_part ? -1 : -2);
+      put_row<T, N>(ws, tp, rsqo, nr + k, xw[0] + sg2 * xw[t], (b2 == B) ? Jo : nullptr, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr, gripper_part ? -1 : -2);
     }
     nr += 4;
   }

@@ -38,6 +38,8 @@ def phase_of(fname, line):
             if line >= ln:
                 cur = nm
         return cur
+    if fname == "gmj_primal.cuh":
+        return "primal solve (gmj_primal.cuh)"
     if fname == "gmj_tail.cuh":
         return "tail (lane 0: stepper, sensors, events, obs)"
     if fname == "gmj_api.cu":

@@ -219,12 +219,12 @@ def main():
         ep_steps.add_(1)
         mask = (done != 0) | (ep_steps >= EPISODE_CAP)
         m8 = mask.to(torch.uint8)
-        gb.reset(m8); gb.spawn_into_scene(0.01, float(np.pi / 2), m8)      # MjEnv.reset: reset -> spawn
+        gb.reset(m8); gb.spawn_with_retry(0.01, float(np.pi / 2), m8)      # MjEnv.reset: reset -> spawn
         ep_steps.mul_((~mask).to(torch.int32))
         launches[0] += 5          # k_step (set_action pass), k_sort_scatter, k_step (combined), k_reset, k_spawn
         return obs, rew, done
 
-    mj.spawn_into_scene(0.01, float(np.pi / 2))
+    mj.batch.spawn_with_retry(0.01, float(np.pi / 2))
     s0 = gb.stats()
     # ---- device-resident timing: K steps, each bracketed by events, L2 flushed between them
     for k in range(W):
@@ -246,7 +246,7 @@ def main():
         ep_steps.add_(1)
         mask = (gb.done != 0) | (ep_steps >= EPISODE_CAP)
         m8 = mask.to(torch.uint8)
-        gb.reset(m8); gb.spawn_into_scene(0.01, float(np.pi / 2), m8)
+        gb.reset(m8); gb.spawn_with_retry(0.01, float(np.pi / 2), m8)
         ep_steps.mul_((~mask).to(torch.int32))
         evs[k][2].record()
         launches[0] += 5          # k_step (set_action pass), k_sort_scatter, k_step (combined), k_reset, k_spawn

@@ -53,6 +53,7 @@ class GripperBatch:
         self.reward = torch.zeros(n, dtype=torch.float32, device=self.device)
         self.done = torch.zeros(n, dtype=torch.uint8, device=self.device)
         self.events = torch.zeros((n, GMJ_EVENT_STATE_LEN), dtype=torch.float32, device=self.device)
+        self.spawned = torch.zeros(n, dtype=torch.uint8, device=self.device)      # spawn_into_scene's return value per env
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
@@ -98,11 +99,13 @@ class GripperBatch:
         xyr = np.stack([np.broadcast_to(np.asarray(v, dtype=np.float32), (n,)) for v in (x, y, zrot)], axis=1)
         xyr = torch.as_tensor(np.ascontiguousarray(xyr), device=self.device)
         m = self._mask(mask)
-        check(self.L.gmj_spawn(self.h, _ptr(idx), _ptr(xyr), _ptr(m), 0.0, 0.0, self._stream()))
+        check(self.L.gmj_spawn(self.h, _ptr(idx), _ptr(xyr), _ptr(m), 0.0, 0.0, _ptr(self.spawned), self._stream()))
 
     def spawn_into_scene(self, xy_range=0.0, rot_range=0.0, mask=None, index=None):
-        """Random pose per env from the device RNG (MjClass::spawn_into_scene); the object too unless `index`
-        (scalar or per-env int array / tensor) names it, as spawn_into_scene(index) does."""
+        """Random pose per env from the device RNG (MjClass::spawn_into_scene: shuffled candidate grid, first pose clear of
+        the fingertips); the object too unless `index` (scalar or per-env int array / tensor) names it, as
+        spawn_into_scene(index) does. Returns the uint8 device tensor `spawned` (1 = placed, 0 = no free candidate: the
+        env has no object); only the masked-in entries are rewritten."""
         m = self._mask(mask)
         idx = None
         if index is not None:
@@ -110,7 +113,35 @@ class GripperBatch:
                 idx = index.to(device=self.device, dtype=torch.int32).expand(self.n_envs).contiguous()
             else:
                 idx = torch.as_tensor(np.broadcast_to(np.asarray(index, dtype=np.int32), (self.n_envs,)).copy(), device=self.device)
-        check(self.L.gmj_spawn(self.h, _ptr(idx), None, _ptr(m), float(xy_range), float(rot_range), self._stream()))
+        check(self.L.gmj_spawn(self.h, _ptr(idx), None, _ptr(m), float(xy_range), float(rot_range), _ptr(self.spawned),
+                               self._stream()))
+        return self.spawned
+
+    def spawn_with_retry(self, xy_range=0.0, rot_range=0.0, mask=None, index=None, tries: int = 3,
+                         fallback_xy_mm: int = 10, fallback_rot_deg: int = 5, generator=None):
+        """MjEnv._spawn_object's policy for the whole batch without a host sync (rl/env/MjEnv.py:1216-1244): up to
+        `tries` calls of spawn_into_scene on the envs still without object, then the "old method" for what is left --
+        a pose on the millimetre grid within +-fallback_xy_mm with one of the base angles 0 / 60 / 120 degrees
+        +-fallback_rot_deg, placed without a collision test (same object when `index` is given, else a fresh draw)."""
+        n = self.n_envs
+        need = torch.ones(n, dtype=torch.uint8, device=self.device) if mask is None else self._mask(mask).clone()
+        for _ in range(tries):
+            ok = self.spawn_into_scene(xy_range, rot_range, need, index)
+            need = need * (1 - ok)
+        g = generator
+        kw = dict(device=self.device) if g is None else dict(device=self.device, generator=g)
+        xy = torch.randint(-fallback_xy_mm, fallback_xy_mm + 1, (n, 2), **kw).to(torch.float32) * 1e-3
+        ang = torch.randint(0, 3, (n,), **kw) * 60 + torch.randint(-fallback_rot_deg, fallback_rot_deg + 1, (n,), **kw)
+        if index is None:
+            idx = torch.randint(0, max(len(self.objects), 1), (n,), **kw).to(torch.int32)
+        elif torch.is_tensor(index):
+            idx = index.to(device=self.device, dtype=torch.int32).expand(n).contiguous()
+        else:
+            idx = torch.as_tensor(np.broadcast_to(np.asarray(index, dtype=np.int32), (n,)).copy(), device=self.device)
+        xyr = torch.cat([xy, (ang.to(torch.float32) * (np.pi / 180.0)).unsqueeze(1)], dim=1).contiguous()
+        check(self.L.gmj_spawn(self.h, _ptr(idx), _ptr(xyr), _ptr(need), 0.0, 0.0, _ptr(self.spawned), self._stream()))
+        self._keep = (idx, xyr, need)          # alive until the launch has read them
+        return need
 
     def step(self, actions, frac=None):
         """Fused set_action -> action_step -> observation / reward / done / events (device tensors)."""

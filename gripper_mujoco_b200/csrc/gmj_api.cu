@@ -5,6 +5,14 @@
 static thread_local std::string g_err;
 void gmj_set_error(const std::string& msg) { g_err = msg; }
 
+// Every entry point makes the handle's device current for its own calls and puts the CALLER'S device back on return
+// (torch and other users of the runtime API rely on the current device staying where they left it).
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
 // counting-sort scatter by load key, heaviest first: envs that owe no lift substeps into perm, the lifting envs
 // into env_list. hist = [counts | cursors | lifter counts | lifter cursors], GMJ_SORT_BUCKETS each.
 template <typename T, int QC>
@@ -105,50 +113,77 @@ __device__ inline int box2d_overlap(const double* a, const double* o, double min
 }
 
 // MjClass::spawn_object / spawn_into_scene (src/mjclass.cpp:2352-2420,2475-2654)
+// Given pose (xyr != NULL): spawn_object, placed unconditionally. Otherwise the reference's search: candidate grid of
+// (x, y) in 2 mm steps within +-xy_range and of rotations in pi/30 steps within +-rot_range, BOTH lists shuffled, walked
+// pairwise for max(n_xy, n_rot) tries; the first pose that is inside the outer bounds and whose rotated footprint
+// clears the three fingertip boxes (taken at reset: target at home, base at the origin, src/mjclass.h:893-904) by 1 mm
+// spawns; when none does the env stays without object and ok[env] = 0 -- the caller retries as MjEnv does
+// (rl/env/MjEnv.py:1216-1244). std::shuffle on the process-global engine becomes a Fisher-Yates walk on the counter RNG
+// (oracle/env.c or_spawn_into_scene draws the same numbers).
+#define GMJ_SPAWN_MAXXY 1024
+#define GMJ_SPAWN_MAXROT 128
+template <typename T, int QC>
+__device__ inline void fy_shuffle(EnvState<T, QC>& e, const DevSettings& S, unsigned short* a, int n) {
+  for (int i = n - 1; i >= 1; i--) {
+    int j = (int)(dev_uniform(e, S) * (float)(i + 1)); if (j > i) j = i;
+    unsigned short t = a[i]; a[i] = a[j]; a[j] = t;
+  }
+}
 template <typename T, int QC>
 __global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const DevSettings* Sp, const GmjObject* objects, int n_objects,
-                        int n_envs, const int32_t* idx, const float* xyr, const uint8_t* mask, float xy_range, float rot_range,
-                        int* err_flag) {
+                        int n_envs, const int32_t* idx, const float* xyr, const uint8_t* mask, double xy_range, double rot_range,
+                        uint8_t* ok_out, int* err_flag) {
   int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= n_envs) return;
   if (mask && !mask[env]) return;
   constexpr int OQ = QC - 8;
   EnvState<T, QC>& e = envs[env];
   const DevSettings& S = *Sp; const DevModelS<T>& M = *Mp;
-  int oi; double x, y, rot;
+  int oi; double x = 0, y = 0, rot = 0;
+  ok_out[env] = 0;
   if (idx) {
     oi = idx[env];
     if (oi < 0 || oi >= n_objects) { if (err_flag) atomicExch(err_flag, 2); return; }
   }
   if (idx && xyr) { x = xyr[3 * env]; y = xyr[3 * env + 1]; rot = xyr[3 * env + 2]; }
   else {
-    // object index (unless given: spawn_into_scene(index), src/mjclass.cpp:2422) and pose from the counter-based
-    // RNG; candidate grid as in spawn_into_scene (2 mm steps within +-xy_range, pi/30 steps within +-rot_range),
-    // fingertip boxes from luke::get_finger_hook_locations (src/myfunctions.cpp:3717-3761), up to 16 candidates
     if (!idx) { oi = (int)(dev_uniform(e, S) * n_objects); if (oi >= n_objects) oi = n_objects - 1; }
     const GmjObject& ob = objects[oi];
     const double inc = 2e-3, rinc = 3.14159265358979323846 / 30.0, gap = 1e-3;
-    int nx = (int)((2 * (double)xy_range) / inc) + 1, nrot = (int)((2 * (double)rot_range) / rinc) + 1;
+    const int num_x = (int)((2 * xy_range) / inc) + 1, num_y = num_x, num_r = (int)((2 * rot_range) / rinc) + 1;
+    const int nxy = num_x * num_y;
+    if (nxy > GMJ_SPAWN_MAXXY || num_r > GMJ_SPAWN_MAXROT) { if (err_flag) atomicExch(err_flag, 3); return; }
     double tips[3][8];
-    const double hook_th = (double)M.hook_angle_deg * (3.14159265358979323846 / 180.000);
-    const double hookx = 0.5 * (double)M.hook_length * sin(hook_th);
-    for (int i = 0; i < 3; i++) {
-      double ang = i * (3.14159265358979323846 * (2.0 / 3.0));
-      double px = -(e.tend.x - hookx) * sin(ang) + e.base_x, py = -(e.tend.x - hookx) * cos(ang) + e.base_y;
-      box2d_init(tips[i], px, py, (double)M.finger_width, (double)M.hook_length, -ang);
+    {
+      DevGripper home; g_reset(home);
+      const double hook_th = (double)M.hook_angle_deg * (3.14159265358979323846 / 180.000);
+      const double hookx = 0.5 * (double)M.hook_length * sin(hook_th);
+      for (int i = 0; i < 3; i++) {
+        double ang = i * (3.14159265358979323846 * (2.0 / 3.0));
+        double px = -(home.x - hookx) * sin(ang) + 0.0, py = -(home.x - hookx) * cos(ang) + 0.0;
+        box2d_init(tips[i], px, py, (double)M.finger_width, (double)M.hook_length, -ang);
+      }
     }
-    x = 0; y = 0; rot = 0;
-    for (int t = 0; t < 16; t++) {
-      int ix = (int)(dev_uniform(e, S) * nx), iy = (int)(dev_uniform(e, S) * nx), ir = (int)(dev_uniform(e, S) * nrot);
-      if (ix >= nx) ix = nx - 1; if (iy >= nx) iy = nx - 1; if (ir >= nrot) ir = nrot - 1;
-      x = nx > 1 ? -(double)xy_range + ix * inc : 0.0; y = nx > 1 ? -(double)xy_range + iy * inc : 0.0;
-      rot = nrot > 1 ? -(double)rot_range + ir * rinc : 0.0;
+    unsigned short pxy[GMJ_SPAWN_MAXXY], pr[GMJ_SPAWN_MAXROT];
+    for (int i = 0; i < nxy; i++) pxy[i] = (unsigned short)i;
+    for (int i = 0; i < num_r; i++) pr[i] = (unsigned short)i;
+    if (nxy > 1) fy_shuffle(e, S, pxy, nxy);
+    if (num_r > 1) fy_shuffle(e, S, pr, num_r);
+    const int tries = nxy > num_r ? nxy : num_r;
+    int found = 0;
+    for (int i = 0; i < tries && !found; i++) {
+      const int k = pxy[i % nxy], ix = k / num_y, iy = k % num_y, ir = pr[i % num_r];
+      x = num_x > 1 ? -xy_range + ix * inc + 0.0 : 0.0;
+      y = num_y > 1 ? -xy_range + iy * inc + 0.0 : 0.0;
+      rot = num_r > 1 ? -rot_range + ir * rinc + 0.0 : 0.0;
       double ours[8];
       box2d_init(ours, x, y, ob.bbox[0], ob.bbox[1], rot);
       int ok = 1;
-      for (int i = 0; i < 3 && ok; i++) if (box2d_overlap(ours, tips[i], gap)) ok = 0;
-      if (ok) break;
+      for (int c = 0; c < 4; c++) if (ours[c] < -100 || ours[c] > 100 || ours[4 + c] < -100 || ours[4 + c] > 100) ok = 0;
+      for (int t = 0; t < 3 && ok; t++) if (box2d_overlap(ours, tips[t], gap)) ok = 0;
+      found = ok;
     }
+    if (!found) return;
   }
   const GmjObject& ob = objects[oi];
   e.obj[0] = (T)ob.type; e.obj[1] = (T)ob.size[0]; e.obj[2] = (T)ob.size[1]; e.obj[3] = (T)ob.size[2]; e.obj[4] = (T)ob.round;
@@ -162,6 +197,7 @@ __global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const Dev
   for (int k = 0; k < 6; k++) e.qvel[OQ + k] = 0;
   e.start_z = (double)(T)z;
   e.nrow_prev = 0; e.mpr_prev = 0;
+  ok_out[env] = 1;
 }
 
 template <typename T, int QC>
@@ -394,7 +430,7 @@ static int launch_step_T(GmjHandle* h, int flags, int nsub, const int32_t* actio
 static int launch_step(GmjHandle* h, int flags, int nsub, const int32_t* actions, const float* frac, float* obs,
                        float* reward, uint8_t* done, float* events, void* stream) {
   if (obs && !h->hs.obs_ok) FAIL("observation unavailable: sensor history deeper than the device ring (GMJ_WIN) or longer than GMJ_MAX_OBS");
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dg_(h->device);
   cudaStream_t st = (cudaStream_t)stream;
   if (h->precision == 0) return launch_step_T<float>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
   return launch_step_T<double>(h, flags, nsub, actions, frac, obs, reward, done, events, st);
@@ -420,24 +456,15 @@ const char* gmj_last_error(void) { return g_err.c_str(); }
 
 int gmj_set_settings(GmjHandle* h, const GmjSettings* settings) {
   if (!h || !settings) FAIL("null argument");
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dg_(h->device);
+  CK(cudaDeviceSynchronize());        // host-synchronising entry point: ordered after everything queued on any stream of the device
   if (build_settings(settings, &h->hs)) return 1;
   { const char* t = getenv("GMJ_ASIN_TAB"); h->hs.asin_tab = (t && atoi(t) == 0) ? nullptr : h->asin_tab; }   // development switch
   CK(cudaMemcpy(h->settings, &h->hs, sizeof(DevSettings), cudaMemcpyHostToDevice));
   return 0;
 }
 
-int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, int device, int precision,
-               uint32_t env_id_offset, GmjHandle** out) {
-  if (!model || !settings || !out || n_envs <= 0) FAIL("bad argument to gmj_create");
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) FAIL("no CUDA device: libgripper_b200 has no CPU fallback");
-  CK(cudaSetDevice(device));
-  GmjHandle* h = new GmjHandle();
-  memset((void*)h, 0, sizeof(*h));
-  h->n_envs = n_envs; h->device = device; h->precision = precision; h->N = model->N; h->B = model->B; h->hm = *model;
-  h->env_id_offset = env_id_offset;
-  h->wide = model->B > 32;
+static int create_impl(GmjHandle* h, const GmjModel* model, const GmjSettings* settings, int n_envs, int device, int precision) {
   {
     int nsm = 0;
     CK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device));
@@ -450,7 +477,7 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
   int rc;
   if (!h->wide) rc = precision == 0 ? upload_model<float, 32>(h, model) : upload_model<double, 32>(h, model);
   else rc = precision == 0 ? upload_model<float, GMJ_WNT>(h, model) : upload_model<double, GMJ_WNT>(h, model);
-  if (rc) { delete h; return 1; }
+  if (rc) return 1;
   CK(cudaMalloc(&h->envs, env_bytes(h) * (size_t)n_envs));
   CK(cudaMemset(h->envs, 0, env_bytes(h) * (size_t)n_envs));
   CK(cudaMalloc(&h->settings, sizeof(DevSettings)));
@@ -466,14 +493,39 @@ int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, i
   CK(cudaMalloc(&h->env_list, sizeof(int) * (size_t)n_envs)); CK(cudaMalloc(&h->env_count, sizeof(int)));
   CK(cudaMemset(h->env_count, 0, sizeof(int)));
   CK(cudaMalloc(&h->perm, sizeof(int) * (size_t)n_envs)); CK(cudaMalloc(&h->hist, sizeof(int) * 4 * GMJ_SORT_BUCKETS));
-  if (gmj_set_settings(h, settings)) { return 1; }
-  *out = h;
+  CK(cudaMalloc(&h->spawn_ok, (size_t)n_envs)); CK(cudaMemset(h->spawn_ok, 0, (size_t)n_envs));
+  if (gmj_set_settings(h, settings)) return 1;
   return gmj_reset(h, nullptr, nullptr);
+}
+
+int gmj_create(const GmjModel* model, const GmjSettings* settings, int n_envs, int device, int precision,
+               uint32_t env_id_offset, GmjHandle** out) {
+  if (!model || !settings || !out || n_envs <= 0) FAIL("bad argument to gmj_create");
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) FAIL("no CUDA device: libgripper_b200 has no CPU fallback");
+  if (device < 0 || device >= ndev) FAIL("gmj_create: no such CUDA device");
+  DeviceGuard dg_(device);
+  GmjHandle* h = new GmjHandle();
+  memset((void*)h, 0, sizeof(*h));
+  h->n_envs = n_envs; h->device = device; h->precision = precision; h->N = model->N; h->B = model->B; h->hm = *model;
+  h->env_id_offset = env_id_offset;
+  h->wide = model->B > 32;
+  if (create_impl(h, model, settings, n_envs, device, precision)) {
+    const std::string keep = g_err;          // every allocation made so far goes back; the first error is the one reported
+    gmj_destroy(h);
+    g_err = keep;
+    return 1;
+  }
+  *out = h;
+  return 0;
 }
 
 int gmj_destroy(GmjHandle* h) {
   if (!h) return 0;
-  cudaSetDevice(h->device);
+  DeviceGuard dg_(h->device);
+  cudaDeviceSynchronize();
+  cudaFree(h->spawn_ok);
   cudaFree(h->envs); cudaFree(h->model); cudaFree(h->settings); cudaFree(h->err_flag); cudaFree(h->stats_dev); cudaFree(h->env_list); cudaFree(h->env_count); cudaFree(h->perm); cudaFree(h->hist); cudaFree(h->asin_tab); cudaFree(h->taps);
   if (h->objects) cudaFree(h->objects);
   if (h->scratch) cudaFree(h->scratch);
@@ -483,7 +535,7 @@ int gmj_destroy(GmjHandle* h) {
 
 int gmj_set_objects(GmjHandle* h, const GmjObject* objects_host, int n_objects) {
   if (!h || !objects_host || n_objects <= 0) FAIL("bad argument to gmj_set_objects");
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dg_(h->device);
   if (h->objects) CK(cudaFree(h->objects));
   CK(cudaMalloc(&h->objects, sizeof(GmjObject) * (size_t)n_objects));
   CK(cudaMemcpy(h->objects, objects_host, sizeof(GmjObject) * (size_t)n_objects, cudaMemcpyHostToDevice));
@@ -493,7 +545,7 @@ int gmj_set_objects(GmjHandle* h, const GmjObject* objects_host, int n_objects) 
 
 int gmj_reset(GmjHandle* h, const uint8_t* mask_dev, void* stream) {
   if (!h) FAIL("null handle");
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dg_(h->device);
   cudaStream_t st = (cudaStream_t)stream;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
   GMJ_FOR_STATE(h, k_reset<T, QC><<<nb, tb, 0, st>>>((EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->settings, h->n_envs, mask_dev, h->env_id_offset));
@@ -501,15 +553,17 @@ int gmj_reset(GmjHandle* h, const uint8_t* mask_dev, void* stream) {
   return 0;
 }
 
-int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const uint8_t* mask_dev, float xy_range,
-              float rot_range, void* stream) {
+int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const uint8_t* mask_dev, double xy_range,
+              double rot_range, uint8_t* ok_dev, void* stream) {
   if (!h) FAIL("null handle");
   if (!h->objects) FAIL("gmj_spawn before gmj_set_objects");
   if (!idx_dev && xyr_dev) FAIL("gmj_spawn: xyr_dev given without idx_dev");
-  CK(cudaSetDevice(h->device));
+  if (xy_range < 0 || rot_range < 0) FAIL("gmj_spawn: negative range");
+  DeviceGuard dg_(h->device);
   cudaStream_t st = (cudaStream_t)stream;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
-  GMJ_FOR_STATE(h, k_spawn<T, QC><<<nb, tb, 0, st>>>((EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->settings, h->objects, h->n_objects, h->n_envs, idx_dev, xyr_dev, mask_dev, xy_range, rot_range, h->err_flag));
+  uint8_t* ok = ok_dev ? ok_dev : h->spawn_ok;
+  GMJ_FOR_STATE(h, k_spawn<T, QC><<<nb, tb, 0, st>>>((EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->settings, h->objects, h->n_objects, h->n_envs, idx_dev, xyr_dev, mask_dev, xy_range, rot_range, ok, h->err_flag));
   CK(cudaGetLastError());
   return 0;
 }
@@ -518,7 +572,7 @@ int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const 
 // lift substeps (quirk Q8: they run INSIDE MjClass::set_action) are recorded in env_list / pending_extra, the
 // others are counting-sorted by expected load.
 static int launch_collect(GmjHandle* h, const int32_t* actions_dev, const float* frac_dev, void* stream) {
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dg_(h->device);
   CK(cudaMemsetAsync(h->env_count, 0, sizeof(int), (cudaStream_t)stream));
   CK(cudaMemsetAsync(h->hist, 0, sizeof(int) * 4 * GMJ_SORT_BUCKETS, (cudaStream_t)stream));
   if (launch_step(h, STEP_SET_ACTION | STEP_COLLECT, 0, actions_dev, frac_dev, nullptr, nullptr, nullptr, nullptr, stream)) return 1;
@@ -570,7 +624,8 @@ static int ensure_scratch(GmjHandle* h, size_t n) {
 
 int gmj_get_state_host(GmjHandle* h, double* qpos_host, double* qvel_host) {
   if (!h) FAIL("null handle");
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dg_(h->device);
+  CK(cudaDeviceSynchronize());        // host-synchronising entry point: ordered after everything queued on any stream of the device
   size_t nq = (size_t)h->n_envs * (h->B + 7), nv = (size_t)h->n_envs * (h->B + 6);
   if (ensure_scratch(h, nq + nv)) return 1;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
@@ -583,7 +638,8 @@ int gmj_get_state_host(GmjHandle* h, double* qpos_host, double* qvel_host) {
 
 int gmj_probe_host(GmjHandle* h, double* probe_host) {
   if (!h || !probe_host) FAIL("null argument");
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dg_(h->device);
+  CK(cudaDeviceSynchronize());        // host-synchronising entry point: ordered after everything queued on any stream of the device
   size_t n = (size_t)h->n_envs * GMJ_PROBE_LEN;
   if (ensure_scratch(h, n)) return 1;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
@@ -603,7 +659,7 @@ static __device__ __align__(256) double g_noalloc_scratch[(size_t)GMJ_NOALLOC_MA
 // In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is looked up
 // once per device, with that device current, and cached here.
 #define GMJ_NOALLOC_MAX_DEVICES 64
-static double* g_noalloc_ptr[GMJ_NOALLOC_MAX_DEVICES];
+static std::atomic<double*> g_noalloc_ptr[GMJ_NOALLOC_MAX_DEVICES];
 
 int gmj_probe_host_noalloc(GmjHandle* h, double* probe_host) {
   if (!h || !probe_host) FAIL("null argument");
@@ -611,13 +667,15 @@ int gmj_probe_host_noalloc(GmjHandle* h, double* probe_host) {
     FAIL("gmj_probe_host_noalloc: n_envs = " + std::to_string(h->n_envs) + " exceeds the static scratch (GMJ_NOALLOC_MAX_ENVS = " +
          std::to_string(GMJ_NOALLOC_MAX_ENVS) + "); use gmj_probe_host");
   if (h->device < 0 || h->device >= GMJ_NOALLOC_MAX_DEVICES) FAIL("gmj_probe_host_noalloc: device index out of range");
-  CK(cudaSetDevice(h->device));
-  if (!g_noalloc_ptr[h->device]) {
+  DeviceGuard dg_(h->device);
+  CK(cudaDeviceSynchronize());        // host-synchronising entry point (no allocation: a sync allocates nothing)
+  double* scratch = g_noalloc_ptr[h->device].load(std::memory_order_acquire);
+  if (!scratch) {
     double* ptr = nullptr;
     CK(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
-    g_noalloc_ptr[h->device] = ptr;
+    g_noalloc_ptr[h->device].store(ptr, std::memory_order_release);     // same address whichever thread wins
+    scratch = ptr;
   }
-  double* scratch = g_noalloc_ptr[h->device];
   const size_t n = (size_t)h->n_envs * GMJ_PROBE_LEN;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
   // k_dump zeroes every probe row before filling it, so nothing of the previous call survives in the rows read back
@@ -634,7 +692,7 @@ int gmj_probe_host_noalloc(GmjHandle* h, double* probe_host) {
 // development build only: per-env cycle counters per phase, uint32[n_envs][12] to the host; clear != 0 zeroes them
 int gmj_prof_host(GmjHandle* h, unsigned int* out_host, int clear) {
   if (!h || !out_host) FAIL("null argument");
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dg_(h->device);
   CK(cudaDeviceSynchronize());
   unsigned int* d = nullptr;
   CK(cudaMalloc(&d, sizeof(unsigned int) * 12 * (size_t)h->n_envs));
@@ -649,7 +707,8 @@ int gmj_prof_host(GmjHandle* h, unsigned int* out_host, int clear) {
 
 int gmj_stats(GmjHandle* h, GmjStats* out) {
   if (!h || !out) FAIL("null argument");
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dg_(h->device);
+  CK(cudaDeviceSynchronize());        // host-synchronising entry point: ordered after everything queued on any stream of the device
   CK(cudaMemset(h->stats_dev, 0, 8 * sizeof(unsigned long long)));
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
   GMJ_FOR_STATE(h, k_stats<T, QC><<<nb, tb>>>((const EnvState<T, QC>*)h->envs, h->n_envs, h->stats_dev));
@@ -660,13 +719,13 @@ int gmj_stats(GmjHandle* h, GmjStats* out) {
   out->rows = (int64_t)v[3]; out->solver_iters = (int64_t)v[4]; out->contact_overflow = (int64_t)v[5];
   int ef = 0;
   CK(cudaMemcpy(&ef, h->err_flag, sizeof(int), cudaMemcpyDeviceToHost));
-  if (ef) { CK(cudaMemset(h->err_flag, 0, sizeof(int))); g_err = ef == 1 ? "an action index was out of range" : "a spawn object index was out of range"; return 2; }
+  if (ef) { CK(cudaMemset(h->err_flag, 0, sizeof(int))); g_err = ef == 1 ? "an action index was out of range" : (ef == 2 ? "a spawn object index was out of range" : "spawn ranges give more candidates than the device search holds (1024 positions, 128 rotations)"); return 2; }
   return 0;
 }
 
 int gmj_set_welds(GmjHandle* h, int mask_on, void* stream) {
   if (!h) FAIL("null handle");
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dg_(h->device);
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
   GMJ_FOR_STATE(h, k_set_welds<T, QC><<<nb, tb, 0, (cudaStream_t)stream>>>((EnvState<T, QC>*)h->envs, h->n_envs, h->B, h->N, mask_on));
   CK(cudaGetLastError());

@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <atomic>
 #include <string>
 #include <vector>
 #include "../../include/gmj.h"
@@ -43,6 +44,7 @@ template <typename E> __device__ __forceinline__ int sort_key_of(const E& e) {
 #define GMJ_WPB_F32_N8 12
 #endif
 
+#define GMJ_MAX_DEVICES 64
 void gmj_set_error(const std::string& msg);      // gmj_api.cu (thread-local last error)
 #define CK(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) { gmj_set_error(std::string(#x) + ": " + cudaGetErrorString(_e)); return 1; } } while (0)
 #define FAIL(msg) do { gmj_set_error(msg); return 1; } while (0)
@@ -65,6 +67,7 @@ struct GmjHandle {
   GmjModel hm;
   size_t smem_bytes;
   double* asin_tab;      // device table for the stepper (DevSettings::asin_tab)
+  uint8_t* spawn_ok;     // per env: 1 when the last gmj_spawn placed its object (spawn_into_scene's return value)
   void* taps;            // T[n_envs][GMJ_MAXTAP][GMJ_TAP_HDR + 3 N]: sensor tap records of the running step (gmj_tail.cuh)
   int n_sm;              // SMs of the device
   int balance_sm;        // SM count when the combined launch balances envs per block over the SMs, 0 = full blocks
@@ -221,8 +224,14 @@ int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, co
   const bool combined = (flags & STEP_COMBINED) != 0;
   constexpr int WPB = StepCfg<T, N>::WPB;
   size_t smem = sizeof(WarpShared<T, N>) * WPB;
-  static bool attr_set = false;
-  if (!attr_set) { CK(cudaFuncSetAttribute(k_step<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
+  // the opt-in to > 48 KB of dynamic shared memory is PER DEVICE: one flag per device (a handle on a second GPU of
+  // the same process would otherwise launch without it and fail)
+  static std::atomic<bool> attr_set[GMJ_MAX_DEVICES];
+  if (h->device < 0 || h->device >= GMJ_MAX_DEVICES) FAIL("device index out of range");
+  if (!attr_set[h->device].load(std::memory_order_acquire)) {
+    CK(cudaFuncSetAttribute(k_step<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set[h->device].store(true, std::memory_order_release);
+  }
   int blocks = (h->n_envs + WPB - 1) / WPB;
   // Few envs (<= 3 rounds of full blocks over the SMs): the step is as long as the chain of 3S substeps of the lifting
   // envs, and a block of 8 warps steps faster than a block of 12 (A/B on B200: +3 % at 4096 envs, -6 % at 16384).
@@ -354,8 +363,12 @@ int launch_step_wide_TN(GmjHandle* h, int flags, int nsub, const int32_t* action
   constexpr int EPB = WideCfg<T, N>::EPB;
   const bool combined = (flags & STEP_COMBINED) != 0;
   size_t smem = sizeof(WideShared<T, N>) * EPB;
-  static bool attr_set = false;
-  if (!attr_set) { CK(cudaFuncSetAttribute(k_step_wide<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
+  static std::atomic<bool> attr_set[GMJ_MAX_DEVICES];       // per device, see launch_step_TN
+  if (h->device < 0 || h->device >= GMJ_MAX_DEVICES) FAIL("device index out of range");
+  if (!attr_set[h->device].load(std::memory_order_acquire)) {
+    CK(cudaFuncSetAttribute(k_step_wide<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set[h->device].store(true, std::memory_order_release);
+  }
   const int blocks = (h->n_envs + EPB - 1) / EPB;
   const int list_blocks = combined ? blocks : 0;        // worst case every env owes a lift; empty list blocks exit at once
   k_step_wide<T, N><<<blocks + list_blocks, GMJ_WNT * EPB, smem, st>>>((EnvState<T, GMJ_WQC>*)h->envs, (const DevModel<T, GMJ_WNT>*)h->model, h->settings,

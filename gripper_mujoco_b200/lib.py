@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GMJ_LIB: development override to A/B-test differently compiled builds of the same sources
 SO_PATH = os.environ.get("GMJ_LIB") or os.path.join(_HERE, "libgripper_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["gmj_api.cu", "gmj_inst.cu", "gmj_step.cuh", "gmj_wide.cuh", "gmj_physics.cuh", "gmj_tail.cuh", "gmj_collide.cuh",
+SOURCES = ["gmj_api.cu", "gmj_inst.cu", "gmj_step.cuh", "gmj_wide.cuh", "gmj_physics.cuh", "gmj_primal.cuh", "gmj_tail.cuh", "gmj_collide.cuh",
            "gmj_device.cuh"]
 HEADERS = [os.path.join(_HERE, "..", "include", h) for h in ("gmj.h", "gmj_types.h")]
 
@@ -122,7 +122,7 @@ def lib():
     L.gmj_set_settings.argtypes = [vp, C.POINTER(GmjSettings)]
     L.gmj_set_objects.argtypes = [vp, C.POINTER(GmjObject), i32]
     L.gmj_reset.argtypes = [vp, vp, vp]
-    L.gmj_spawn.argtypes = [vp, vp, vp, vp, f32, f32, vp]
+    L.gmj_spawn.argtypes = [vp, vp, vp, vp, C.c_double, C.c_double, vp, vp]
     L.gmj_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
     L.gmj_set_action.argtypes = [vp, vp, vp, vp]
     L.gmj_action_step.argtypes = [vp, vp]

@@ -143,16 +143,17 @@ class MjClass:
         self.batch.spawn_object(index, x, y, zrot, mask)
 
     def spawn_into_scene(self, xrange=None, rotrange=None, mask=None, index=None):
-        """spawn_into_scene() / spawn_into_scene(index) (src/mjclass.cpp:2422-2654); always finds a pose here
-        (the device sampler falls back to its last candidate), so there is no `False` return to retry on."""
+        """spawn_into_scene() / spawn_into_scene(index) (src/mjclass.cpp:2422-2654). Returns a bool tensor [n_envs]:
+        True where an object was placed, False where no candidate pose was clear of the fingertips (the reference's
+        `return false`; MjEnv retries, rl/env/MjEnv.py:1216-1244). Entries outside `mask` keep their last value."""
         d = self.default_spawn_params
         if index is not None and not torch.is_tensor(index):
             n = len(self._objects)
             if np.any(np.asarray(index) < 0) or np.any(np.asarray(index) >= n):
                 raise RuntimeError("bad index to spawn_into_scene()")
-        self.batch.spawn_into_scene(d.xrange if xrange is None else xrange,
-                                    d.rotrange if rotrange is None else rotrange, mask, index)
-        return True
+        ok = self.batch.spawn_into_scene(d.xrange if xrange is None else xrange,
+                                         d.rotrange if rotrange is None else rotrange, mask, index)
+        return ok.bool()
 
     def get_number_of_objects(self) -> int:
         return len(self._objects)

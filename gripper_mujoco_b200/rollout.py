@@ -339,7 +339,7 @@ class VectorRollout:
 
     def reset_all(self):
         self.mj.reset()
-        self.mj.spawn_into_scene(self.spawn_xy_range, self.spawn_rot_range)
+        self.mj.batch.spawn_with_retry(self.spawn_xy_range, self.spawn_rot_range)
         self.obs = self.mj.get_observation().clone()
         self.ep_steps.zero_(); self.ep_return.zero_()
         return self.obs
@@ -364,7 +364,7 @@ class VectorRollout:
         self.returns_sum += (self.ep_return * finished).sum(dtype=torch.float64)
         self.lengths_sum += (self.ep_steps * finished).sum(dtype=torch.float64)
         m8 = finished.to(torch.uint8)
-        gb.reset(m8); gb.spawn_into_scene(self.spawn_xy_range, self.spawn_rot_range, m8)
+        gb.reset(m8); gb.spawn_with_retry(self.spawn_xy_range, self.spawn_rot_range, m8)
         fresh = self.mj.get_observation()
         self.obs = torch.where(finished.unsqueeze(1), fresh, new_obs)
         keep = (~finished)

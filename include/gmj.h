@@ -4,7 +4,10 @@
  * Every entry point returns 0 on success, non-zero on error (gmj_last_error() gives the text).
  * All pointers named *_dev are DEVICE pointers on the handle's GPU, all pointers named *_host are
  * host pointers; the library owns every piece of simulation state, the caller owns in/out buffers.
- * No entry point synchronises the host except gmj_*_host() and gmj_stats().
+ * No entry point synchronises the host except gmj_*_host(), gmj_stats(), gmj_set_settings() and gmj_destroy(): those
+ * call cudaDeviceSynchronize() first, so they are ordered after work queued on ANY stream of the device (also streams
+ * created cudaStreamNonBlocking). Every entry point leaves the caller's current CUDA device as it found it. Handles on
+ * several devices may live in one process (one handle per GPU).
  *
  * Reference interface each entry replaces (path:line in lukebeddow/gripper-mujoco):
  *   gmj_create / gmj_destroy     MjClass::MjClass / load / init        src/mjclass.cpp:22-79,377-409 ; src/bind.cpp:43-52
@@ -18,8 +21,8 @@
  *   gmj_action_step              MjClass::action_step                   src/mjclass.cpp:1483-1508
  *   gmj_substeps                 MjClass::step (n times)                src/mjclass.cpp:504-530 ; src/bind.cpp:57
  *   gmj_observe                  get_observation / reward / is_done / get_event_state
- *   gmj_get_state                data->qpos / qvel reads (parity dumps)
- *   gmj_probe                    read_armadillo_gauge / sim_sensors_SI_ latest / calibrate_reset
+ *   gmj_get_state_host           data->qpos / qvel reads (parity dumps)
+ *   gmj_probe_host               read_armadillo_gauge / sim_sensors_SI_ latest / calibrate_reset
  *   gmj_stats                    (new) solver + stability counters, mirrors BADQACC src/myfunctions.cpp:4233
  */
 #ifndef GMJ_H_
@@ -41,16 +44,18 @@ int gmj_destroy(GmjHandle* h);
 int gmj_set_settings(GmjHandle* h, const GmjSettings* settings);
 int gmj_set_objects(GmjHandle* h, const GmjObject* objects_host, int n_objects);
 
-/* mask_dev: uint8[n_envs] (NULL = all). episode_dev: uint32[n_envs] episode counters or NULL
- * (NULL = per-env counter kept by the library). stream: cudaStream_t as void*. */
+/* mask_dev: uint8[n_envs] (NULL = all): MjClass::reset of the selected envs. Each env keeps its own episode counter
+ * (it keys the counter RNG: draw counter = episode << 12). stream: cudaStream_t as void*. */
 int gmj_reset(GmjHandle* h, const uint8_t* mask_dev, void* stream);
-/* idx_dev int32[n_envs], xyr_dev float[n_envs][3] (x, y, z-rotation); idx_dev == NULL draws object,
- * position (2 mm grid within +-xy_range) and rotation (pi/30 grid within +-rot_range) per env from the
- * counter-based RNG, rejecting poses that overlap the fingertip boxes (spawn_into_scene,
- * src/mjclass.cpp:2475-2654). idx_dev given with xyr_dev == NULL: that object at a random pose
- * (spawn_into_scene(index), src/mjclass.cpp:2422-2473). mask_dev as above. */
+/* idx_dev int32[n_envs], xyr_dev float[n_envs][3] (x, y, z-rotation): spawn_object, placed unconditionally.
+ * xyr_dev == NULL: spawn_into_scene -- the reference's search (src/mjclass.cpp:2475-2654): candidate (x, y) on a 2 mm
+ * grid within +-xy_range and rotations on a pi/30 grid within +-rot_range, both lists shuffled (counter RNG) and walked
+ * pairwise; the first pose whose footprint clears the three fingertip boxes by 1 mm spawns. idx_dev == NULL draws the
+ * object per env as well. ok_dev uint8[n_envs] or NULL: 1 where an object was placed, 0 where no candidate was free
+ * (spawn_into_scene's `false`: the env has no object, the caller retries / falls back as rl/env/MjEnv.py:1216-1244).
+ * mask_dev as above; ok_dev is written for masked-in envs only. */
 int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const uint8_t* mask_dev,
-              float xy_range, float rot_range, void* stream);
+              double xy_range, double rot_range, uint8_t* ok_dev, void* stream);
 
 /* fused hot path: actions_dev int32[n_envs] (discrete action index), frac_dev float[n_envs] or NULL.
  * Outputs (any may be NULL): obs_dev float[n_envs][n_obs], reward_dev float[n_envs],
@@ -78,15 +83,16 @@ enum { GP_time = 0, GP_wrist_z, GP_gauge0, GP_gauge1, GP_gauge2, GP_si_gauge0, G
        GMJ_PROBE_LEN = 32 };
 int gmj_probe_host(GmjHandle* h, double* probe_host);
 /* Allocation-free variant of gmj_probe_host. No counterpart in the reference: added
- * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
- * it). The device scratch is a static 4 MiB array inside the library (held by every GPU that loads it, until exit),
+ * operators for callers that cannot call cudaMalloc (tight serving loops, harnesses that forbid allocation; NOT
+ * usable while a stream is being captured: it synchronises and copies to pageable host memory). The device scratch is a static 4 MiB array inside the library (held by every GPU that loads it, until exit),
  * so n_envs <= GMJ_NOALLOC_MAX_ENVS; larger handles are rejected with an error. It calls no cudaMalloc / cudaFree. All
  * calls on a device share the array: calls that overlap on the GPU race; results equal gmj_probe_host's. */
 #define GMJ_NOALLOC_MAX_ENVS 16384
 int gmj_probe_host_noalloc(GmjHandle* h, double* probe_host);
 int gmj_stats(GmjHandle* h, GmjStats* out);
-/* overwrite joint positions of all envs with qpos (host, double[nq]) and zero velocities: used by the
- * calibration flow (calibrate_reset writes qpos directly, src/myfunctions.cpp:1497-1516) */
+/* luke::set_all_constraints / apply_segment_force's weld locking (src/myfunctions.cpp:1157-1170,1642-1727): switch the
+ * welds in mask_on (bits 0-2 prismatic, 3-5 revolute, 6 palm) on with their anchors at the current joint values, the
+ * others off, in every env. Used by the gauge calibration (tip load with the motor joints locked). */
 int gmj_set_welds(GmjHandle* h, int mask_on, void* stream);
 const char* gmj_last_error(void);
 

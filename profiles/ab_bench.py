@@ -27,7 +27,7 @@ st.bending_gauge.normalise = {5: 2.41, 8: 2.54, 16: 2.63, 24: 2.66}[N]
 st.wrist_sensor_Z.raw_value_offset = -23.3
 mj = MjClass(n, GripperParams(num_segments=N), settings=st, calibrate=False)
 gb = mj.batch
-mj.spawn_into_scene(0.01, float(np.pi / 2))
+mj.batch.spawn_with_retry(0.01, float(np.pi / 2))
 g = torch.Generator(device="cpu"); g.manual_seed(0)
 acts = torch.randint(0, mj.get_n_actions(), (W + K, n), generator=g, dtype=torch.int32).to(mj.device)
 ep = torch.zeros(n, dtype=torch.int32, device=mj.device)
@@ -41,7 +41,7 @@ for k in range(W + K):
     ep.add_(1)
     mask = (gb.done != 0) | (ep >= 250)
     m8 = mask.to(torch.uint8)
-    gb.reset(m8); gb.spawn_into_scene(0.01, float(np.pi / 2), m8)
+    gb.reset(m8); gb.spawn_with_retry(0.01, float(np.pi / 2), m8)
     ep.mul_((~mask).to(torch.int32))
 torch.cuda.synchronize()
 ms = [a.elapsed_time(b) for a, b in evs]

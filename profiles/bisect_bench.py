@@ -11,7 +11,7 @@ def run(term, resets, steps=40, n=4096):
     st.mujoco_timestep, st.sim_steps_per_action = 6.825e-3, 30
     st.bending_gauge.normalise = 2.41; st.wrist_sensor_Z.raw_value_offset = -23.3
     mj = MjClass(n, GripperParams(num_segments=5), settings=st, calibrate=False)
-    mj.spawn_into_scene(0.01, float(np.pi / 2))
+    mj.batch.spawn_with_retry(0.01, float(np.pi / 2))
     g = torch.Generator(device="cpu"); g.manual_seed(0)
     acts = torch.randint(0, mj.get_n_actions() - (0 if term else 1), (steps, n), generator=g, dtype=torch.int32).to(mj.device)
     gb = mj.batch
@@ -21,7 +21,7 @@ def run(term, resets, steps=40, n=4096):
         e0.record(); gb.step(acts[k]); e1.record()
         if resets:
             m8 = (gb.done != 0).to(torch.uint8)
-            gb.reset(m8); gb.spawn_into_scene(0.01, float(np.pi / 2), m8)
+            gb.reset(m8); gb.spawn_with_retry(0.01, float(np.pi / 2), m8)
         torch.cuda.synchronize()
         if k >= 10: tot += e0.elapsed_time(e1)
     s = gb.stats()

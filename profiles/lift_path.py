@@ -11,7 +11,7 @@ def run(n, term, steps=12):
     st.mujoco_timestep, st.sim_steps_per_action = 6.825e-3, 30
     st.bending_gauge.normalise = 2.41; st.wrist_sensor_Z.raw_value_offset = -23.3
     mj = MjClass(n, GripperParams(num_segments=5), settings=st, calibrate=False)
-    mj.spawn_into_scene(0.01, float(np.pi / 2))
+    mj.batch.spawn_with_retry(0.01, float(np.pi / 2))
     gb = mj.batch
     g = torch.Generator(device="cpu"); g.manual_seed(0)
     warm = torch.randint(0, 14, (6, n), generator=g, dtype=torch.int32).to(mj.device)
@@ -21,7 +21,7 @@ def run(n, term, steps=12):
     for k in range(steps):
         m8 = torch.ones(n, dtype=torch.uint8, device=mj.device)
         if term:
-            gb.reset(m8); gb.spawn_into_scene(0.01, float(np.pi / 2), m8); gb.step(warm[k % 6])
+            gb.reset(m8); gb.spawn_with_retry(0.01, float(np.pi / 2), m8); gb.step(warm[k % 6])
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); gb.step(a); e1.record(); torch.cuda.synchronize()
         tot += e0.elapsed_time(e1)

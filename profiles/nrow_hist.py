@@ -10,7 +10,7 @@ st = Settings(); st.debug = False; st.random_seed = 1234; st.set_use_noise(True)
 st.mujoco_timestep, st.sim_steps_per_action = 6.825e-3, 30
 st.bending_gauge.normalise = 2.41; st.wrist_sensor_Z.raw_value_offset = -23.3
 mj = MjClass(n, GripperParams(num_segments=5), settings=st, calibrate=False)
-mj.spawn_into_scene(0.01, float(np.pi / 2))
+mj.batch.spawn_with_retry(0.01, float(np.pi / 2))
 g = torch.Generator(device="cpu"); g.manual_seed(0)
 gb = mj.batch
 H = np.zeros(50, dtype=np.int64)
@@ -18,7 +18,7 @@ for k in range(60):
     a = torch.randint(0, 15, (n,), generator=g, dtype=torch.int32)
     gb.step(a)
     m8 = (gb.done != 0).to(torch.uint8)
-    gb.reset(m8); gb.spawn_into_scene(0.01, float(np.pi / 2), m8)
+    gb.reset(m8); gb.spawn_with_retry(0.01, float(np.pi / 2), m8)
     if k >= 20:
         nr = gb.probe()[:, GP["nrow"]].astype(int)
         H += np.bincount(nr, minlength=50)[:50]

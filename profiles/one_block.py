@@ -10,7 +10,7 @@ st = Settings(); st.debug = False; st.random_seed = 1234; st.set_use_noise(True)
 st.mujoco_timestep, st.sim_steps_per_action = 6.825e-3, 30
 st.bending_gauge.normalise = 2.41; st.wrist_sensor_Z.raw_value_offset = -23.3
 mj = MjClass(n, GripperParams(num_segments=5), settings=st, calibrate=False)
-mj.spawn_into_scene(0.01, float(np.pi / 2))
+mj.batch.spawn_with_retry(0.01, float(np.pi / 2))
 g = torch.Generator(device="cpu"); g.manual_seed(0)
 acts = torch.randint(0, 14, (16, n), generator=g, dtype=torch.int32).to(mj.device)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -24,7 +24,7 @@ st.mujoco_timestep, st.sim_steps_per_action = ({5: 7.02e-3, 8: 3.262e-3, 16: 1.0
 st.bending_gauge.normalise = {5: 2.41, 8: 2.54, 16: 2.63, 24: 2.66}[N]
 st.wrist_sensor_Z.raw_value_offset = -23.3
 mj = MjClass(n, GripperParams(num_segments=N), settings=st, calibrate=False)
-mj.spawn_into_scene(0.01, float(np.pi / 2))
+mj.batch.spawn_with_retry(0.01, float(np.pi / 2))
 g = torch.Generator(device="cpu"); g.manual_seed(0)
 acts = torch.randint(0, mj.get_n_actions() - 1, (steps, n), generator=g, dtype=torch.int32).to(mj.device)
 ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

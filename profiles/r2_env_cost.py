@@ -16,7 +16,7 @@ mj = MjClass(n, GripperParams(num_segments=5), settings=st, calibrate=False)
 gb = mj.batch
 L = gb.L
 L.gmj_prof_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
-mj.spawn_into_scene(0.01, float(np.pi / 2))
+mj.batch.spawn_with_retry(0.01, float(np.pi / 2))
 g = torch.Generator(device="cpu"); g.manual_seed(0)
 K = 24
 acts = torch.randint(0, 15 if lift else 14, (K, n), generator=g, dtype=torch.int32).to(mj.device)
@@ -31,7 +31,7 @@ for k in range(K):
     gb.step(acts[k])
     if lift:
         ep.add_(1); mask = (gb.done != 0) | (ep >= 250); m8 = mask.to(torch.uint8)
-        gb.reset(m8); gb.spawn_into_scene(0.01, float(np.pi / 2), m8); ep.mul_((~mask).to(torch.int32))
+        gb.reset(m8); gb.spawn_with_retry(0.01, float(np.pi / 2), m8); ep.mul_((~mask).to(torch.int32))
 e1.record(); torch.cuda.synchronize()
 L.gmj_prof_host(gb.h, prof.ctypes.data, 0)
 s1 = gb.stats()

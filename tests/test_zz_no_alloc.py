@@ -25,7 +25,7 @@ def test_noalloc_probe_equals_probe_on_two_calls_in_a_row():
     big, gb = _batch(300), _batch(37)
     rng = np.random.default_rng(0)
     for b in (big, gb):
-        b.reset(); b.spawn_into_scene(0.01, 0.5)
+        b.reset(); b.spawn_with_retry(0.01, 0.5)
     big.step(rng.integers(0, big.n_actions - 1, big.n_envs).astype(np.int32))
     stale = big.probe_noalloc()                      # fills 300 rows of the shared scratch
     assert np.array_equal(stale, big.probe())

@@ -99,7 +99,14 @@ class GripperBatch:
         xyr = np.stack([np.broadcast_to(np.asarray(v, dtype=np.float32), (n,)) for v in (x, y, zrot)], axis=1)
         xyr = torch.as_tensor(np.ascontiguousarray(xyr), device=self.device)
         m = self._mask(mask)
-        check(self.L.gmj_spawn(self.h, _ptr(idx), _ptr(xyr), _ptr(m), 0.0, 0.0, _ptr(self.spawned), self._stream()))
+        check(self.L.gmj_spawn(self.h, _ptr(idx), _ptr(xyr), _ptr(m), 0.0, 0.0, 1, -1, 0, _ptr(self.spawned), self._stream()))
+
+    def _index_tensor(self, index):
+        if index is None:
+            return None
+        if torch.is_tensor(index):
+            return index.to(device=self.device, dtype=torch.int32).expand(self.n_envs).contiguous()
+        return torch.as_tensor(np.broadcast_to(np.asarray(index, dtype=np.int32), (self.n_envs,)).copy(), device=self.device)
 
     def spawn_into_scene(self, xy_range=0.0, rot_range=0.0, mask=None, index=None):
         """Random pose per env from the device RNG (MjClass::spawn_into_scene: shuffled candidate grid, first pose clear of
@@ -107,41 +114,33 @@ class GripperBatch:
         spawn_into_scene(index) does. Returns the uint8 device tensor `spawned` (1 = placed, 0 = no free candidate: the
         env has no object); only the masked-in entries are rewritten."""
         m = self._mask(mask)
-        idx = None
-        if index is not None:
-            if torch.is_tensor(index):
-                idx = index.to(device=self.device, dtype=torch.int32).expand(self.n_envs).contiguous()
-            else:
-                idx = torch.as_tensor(np.broadcast_to(np.asarray(index, dtype=np.int32), (self.n_envs,)).copy(), device=self.device)
-        check(self.L.gmj_spawn(self.h, _ptr(idx), None, _ptr(m), float(xy_range), float(rot_range), _ptr(self.spawned),
-                               self._stream()))
+        idx = self._index_tensor(index)
+        check(self.L.gmj_spawn(self.h, _ptr(idx), None, _ptr(m), float(xy_range), float(rot_range), 1, -1, 0,
+                               _ptr(self.spawned), self._stream()))
+        self._keep = (idx, m)
         return self.spawned
 
     def spawn_with_retry(self, xy_range=0.0, rot_range=0.0, mask=None, index=None, tries: int = 3,
-                         fallback_xy_mm: int = 10, fallback_rot_deg: int = 5, generator=None):
-        """MjEnv._spawn_object's policy for the whole batch without a host sync (rl/env/MjEnv.py:1216-1244): up to
-        `tries` calls of spawn_into_scene on the envs still without object, then the "old method" for what is left --
-        a pose on the millimetre grid within +-fallback_xy_mm with one of the base angles 0 / 60 / 120 degrees
-        +-fallback_rot_deg, placed without a collision test (same object when `index` is given, else a fresh draw)."""
-        n = self.n_envs
-        need = torch.ones(n, dtype=torch.uint8, device=self.device) if mask is None else self._mask(mask).clone()
-        for _ in range(tries):
-            ok = self.spawn_into_scene(xy_range, rot_range, need, index)
-            need = need * (1 - ok)
-        g = generator
-        kw = dict(device=self.device) if g is None else dict(device=self.device, generator=g)
-        xy = torch.randint(-fallback_xy_mm, fallback_xy_mm + 1, (n, 2), **kw).to(torch.float32) * 1e-3
-        ang = torch.randint(0, 3, (n,), **kw) * 60 + torch.randint(-fallback_rot_deg, fallback_rot_deg + 1, (n,), **kw)
-        if index is None:
-            idx = torch.randint(0, max(len(self.objects), 1), (n,), **kw).to(torch.int32)
-        elif torch.is_tensor(index):
-            idx = index.to(device=self.device, dtype=torch.int32).expand(n).contiguous()
-        else:
-            idx = torch.as_tensor(np.broadcast_to(np.asarray(index, dtype=np.int32), (n,)).copy(), device=self.device)
-        xyr = torch.cat([xy, (ang.to(torch.float32) * (np.pi / 180.0)).unsqueeze(1)], dim=1).contiguous()
-        check(self.L.gmj_spawn(self.h, _ptr(idx), _ptr(xyr), _ptr(need), 0.0, 0.0, _ptr(self.spawned), self._stream()))
-        self._keep = (idx, xyr, need)          # alive until the launch has read them
-        return need
+                         fallback_xy_mm: int = 10, fallback_rot_deg: int = 5):
+        """MjEnv._spawn_object's policy for the whole batch in ONE launch (rl/env/MjEnv.py:1216-1244): up to `tries`
+        spawn_into_scene attempts per env, then the "old method" for an env still without a free pose -- a pose on the
+        millimetre grid within +-fallback_xy_mm with a base angle of 0 / 60 / 120 degrees +-fallback_rot_deg, placed
+        without a collision test. `spawned` afterwards: 1 = placed by the search, 2 = by the fallback."""
+        m = self._mask(mask)
+        idx = self._index_tensor(index)
+        check(self.L.gmj_spawn(self.h, _ptr(idx), None, _ptr(m), float(xy_range), float(rot_range), int(tries),
+                               int(fallback_xy_mm), int(fallback_rot_deg), _ptr(self.spawned), self._stream()))
+        self._keep = (idx, m)
+        return self.spawned
+
+    def reset_done(self, done=None, step_cap: int = 250):
+        """MjEnv.step's end-of-episode rule on the device: reset the envs whose done flag is set or whose episode reached
+        `step_cap` action steps; returns the uint8 device mask of the envs that were reset (gmj_reset_done)."""
+        d = self.done if done is None else self._mask(done)
+        if not hasattr(self, "_reset_mask"):
+            self._reset_mask = torch.zeros(self.n_envs, dtype=torch.uint8, device=self.device)
+        check(self.L.gmj_reset_done(self.h, _ptr(d), int(step_cap), _ptr(self._reset_mask), self._stream()))
+        return self._reset_mask
 
     def step(self, actions, frac=None):
         """Fused set_action -> action_step -> observation / reward / done / events (device tensors)."""
@@ -191,6 +190,15 @@ class GripperBatch:
         p = np.zeros((self.n_envs, GMJ_PROBE_LEN)) if out is None else out
         check(self.L.gmj_probe_host_noalloc(self.h, p.ctypes.data_as(C.c_void_p)))
         return p
+
+    def event_track(self):
+        """(row [n, 36], abs [n, 36], last_value [n, 36], cumulative_reward [n]) of env_.cnt, events in X-macro order."""
+        torch.cuda.synchronize(self.device)
+        ra = np.zeros((self.n_envs, 36, 2), dtype=np.int32); last = np.zeros((self.n_envs, 36), dtype=np.float32)
+        cr = np.zeros(self.n_envs, dtype=np.float32)
+        check(self.L.gmj_event_track_host(self.h, ra.ctypes.data_as(C.c_void_p), last.ctypes.data_as(C.c_void_p),
+                                          cr.ctypes.data_as(C.c_void_p)))
+        return ra[:, :, 0], ra[:, :, 1], last, cr
 
     def probe_field(self, name):
         return self.probe()[:, GP[name]]

@@ -35,12 +35,17 @@ __global__ void k_sort_scatter(const EnvState<T, QC>* __restrict__ envs, int n_e
 // MjClass::reset + luke::reset (src/mjclass.cpp:434-486, src/myfunctions.cpp:544-570): one thread per env
 template <typename T, int QC>
 __global__ void k_reset(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const DevSettings* Sp, int n_envs,
-                        const uint8_t* mask, uint32_t env_id_offset) {
+                        const uint8_t* mask, uint32_t env_id_offset, int step_cap, uint8_t* mask_out) {
   constexpr int OQ = QC - 8;
   int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= n_envs) return;
-  if (mask && !mask[env]) return;
   EnvState<T, QC>& e = envs[env];
+  // gmj_reset_done: the env resets when its done flag is set OR its episode reached step_cap action steps (MjEnv.step's
+  // truncation, rl/env/MjEnv.py:616-637); the resolved mask goes out for the spawn that follows
+  bool go = !mask || mask[env];
+  if (step_cap > 0) go = (mask && mask[env]) || e.num_action_steps >= step_cap;
+  if (mask_out) mask_out[env] = go ? 1 : 0;
+  if (!go) return;
   const DevModelS<T>& M = *Mp; const DevSettings& S = *Sp;
   const int N = M.N, NL = N + 2, B = M.B;
   uint32_t episode = e.episode + 1;
@@ -132,7 +137,7 @@ __device__ inline void fy_shuffle(EnvState<T, QC>& e, const DevSettings& S, unsi
 template <typename T, int QC>
 __global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const DevSettings* Sp, const GmjObject* objects, int n_objects,
                         int n_envs, const int32_t* idx, const float* xyr, const uint8_t* mask, double xy_range, double rot_range,
-                        uint8_t* ok_out, int* err_flag) {
+                        int tries_max, int fb_xy_mm, int fb_rot_deg, uint8_t* ok_out, int* err_flag) {
   int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= n_envs) return;
   if (mask && !mask[env]) return;
@@ -145,7 +150,7 @@ __global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const Dev
     oi = idx[env];
     if (oi < 0 || oi >= n_objects) { if (err_flag) atomicExch(err_flag, 2); return; }
   }
-  if (idx && xyr) { x = xyr[3 * env]; y = xyr[3 * env + 1]; rot = xyr[3 * env + 2]; }
+  if (idx && xyr) { x = xyr[3 * env]; y = xyr[3 * env + 1]; rot = xyr[3 * env + 2]; ok_out[env] = 1; }
   else {
     if (!idx) { oi = (int)(dev_uniform(e, S) * n_objects); if (oi >= n_objects) oi = n_objects - 1; }
     const GmjObject& ob = objects[oi];
@@ -165,12 +170,14 @@ __global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const Dev
       }
     }
     unsigned short pxy[GMJ_SPAWN_MAXXY], pr[GMJ_SPAWN_MAXROT];
+    int found = 0;
+    // MjEnv._spawn_object: up to tries_max calls of spawn_into_scene (each with fresh shuffles), rl/env/MjEnv.py:1216-1227
+    for (int attempt = 0; attempt < tries_max && !found; attempt++) {
     for (int i = 0; i < nxy; i++) pxy[i] = (unsigned short)i;
     for (int i = 0; i < num_r; i++) pr[i] = (unsigned short)i;
     if (nxy > 1) fy_shuffle(e, S, pxy, nxy);
     if (num_r > 1) fy_shuffle(e, S, pr, num_r);
     const int tries = nxy > num_r ? nxy : num_r;
-    int found = 0;
     for (int i = 0; i < tries && !found; i++) {
       const int k = pxy[i % nxy], ix = k / num_y, iy = k % num_y, ir = pr[i % num_r];
       x = num_x > 1 ? -xy_range + ix * inc + 0.0 : 0.0;
@@ -183,7 +190,20 @@ __global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const Dev
       for (int t = 0; t < 3 && ok; t++) if (box2d_overlap(ours, tips[t], gap)) ok = 0;
       found = ok;
     }
-    if (!found) return;
+    }
+    if (!found) {
+      if (fb_xy_mm < 0) return;
+      // "old method" of MjEnv._spawn_object (rl/env/MjEnv.py:1229-1244): a pose on the millimetre grid with one of the
+      // base angles 0 / 60 / 120 degrees +- fb_rot_deg, placed without a collision test
+      int xm = (int)(dev_uniform(e, S) * (float)(2 * fb_xy_mm + 1)); if (xm > 2 * fb_xy_mm) xm = 2 * fb_xy_mm;
+      int ym = (int)(dev_uniform(e, S) * (float)(2 * fb_xy_mm + 1)); if (ym > 2 * fb_xy_mm) ym = 2 * fb_xy_mm;
+      int an = (int)(dev_uniform(e, S) * (float)(2 * fb_rot_deg + 1)); if (an > 2 * fb_rot_deg) an = 2 * fb_rot_deg;
+      int bi = (int)(dev_uniform(e, S) * 3.0f); if (bi > 2) bi = 2;
+      x = (xm - fb_xy_mm) * 1e-3; y = (ym - fb_xy_mm) * 1e-3;
+      rot = (60 * bi + an - fb_rot_deg) * (3.14159265358979323846 / 180.0);
+      found = 2;
+    }
+    ok_out[env] = (uint8_t)found;
   }
   const GmjObject& ob = objects[oi];
   e.obj[0] = (T)ob.type; e.obj[1] = (T)ob.size[0]; e.obj[2] = (T)ob.size[1]; e.obj[3] = (T)ob.size[2]; e.obj[4] = (T)ob.round;
@@ -197,7 +217,6 @@ __global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const Dev
   for (int k = 0; k < 6; k++) e.qvel[OQ + k] = 0;
   e.start_z = (double)(T)z;
   e.nrow_prev = 0; e.mpr_prev = 0;
-  ok_out[env] = 1;
 }
 
 template <typename T, int QC>
@@ -253,6 +272,20 @@ __global__ void k_stats(const EnvState<T, QC>* envs, int n_envs, unsigned long l
   atomicAdd(&out[0], e.st_substeps); atomicAdd(&out[1], (unsigned long long)(e.st_unstable + (e.unstable ? 1 : 0)));
   atomicAdd(&out[2], e.st_contacts); atomicAdd(&out[3], e.st_rows); atomicAdd(&out[4], e.st_iters);
   atomicAdd(&out[5], (unsigned long long)e.st_overflow);
+}
+
+// EventTrack of every env (MjType::EventTrack, src/mjclass.h:575-647): row / abs counters and last values
+template <typename T, int QC>
+__global__ void k_event_track(const EnvState<T, QC>* envs, int n_envs, int32_t* row_abs, float* last, float* cum_reward) {
+  int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= n_envs) return;
+  const EnvState<T, QC>& e = envs[env];
+  constexpr int NE = GBE_COUNT + GLE_COUNT;
+  for (int k = 0; k < NE; k++) {
+    row_abs[((size_t)env * NE + k) * 2] = e.ev_row[k]; row_abs[((size_t)env * NE + k) * 2 + 1] = e.ev_abs[k];
+    last[(size_t)env * NE + k] = e.ev_last[k];
+  }
+  cum_reward[env] = e.cumulative_reward;
 }
 
 #ifdef GMJ_PROF
@@ -548,22 +581,35 @@ int gmj_reset(GmjHandle* h, const uint8_t* mask_dev, void* stream) {
   DeviceGuard dg_(h->device);
   cudaStream_t st = (cudaStream_t)stream;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
-  GMJ_FOR_STATE(h, k_reset<T, QC><<<nb, tb, 0, st>>>((EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->settings, h->n_envs, mask_dev, h->env_id_offset));
+  GMJ_FOR_STATE(h, k_reset<T, QC><<<nb, tb, 0, st>>>((EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->settings, h->n_envs, mask_dev, h->env_id_offset, 0, nullptr));
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int gmj_reset_done(GmjHandle* h, const uint8_t* done_dev, int step_cap, uint8_t* mask_out_dev, void* stream) {
+  if (!h || !done_dev) FAIL("gmj_reset_done: null handle or done flags");
+  if (step_cap <= 0) FAIL("gmj_reset_done: step_cap must be positive");
+  DeviceGuard dg_(h->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  int tb = 128, nb = (h->n_envs + tb - 1) / tb;
+  GMJ_FOR_STATE(h, k_reset<T, QC><<<nb, tb, 0, st>>>((EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->settings, h->n_envs, done_dev, h->env_id_offset, step_cap, mask_out_dev));
   CK(cudaGetLastError());
   return 0;
 }
 
 int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const uint8_t* mask_dev, double xy_range,
-              double rot_range, uint8_t* ok_dev, void* stream) {
+              double rot_range, int tries, int fallback_xy_mm, int fallback_rot_deg, uint8_t* ok_dev, void* stream) {
   if (!h) FAIL("null handle");
   if (!h->objects) FAIL("gmj_spawn before gmj_set_objects");
   if (!idx_dev && xyr_dev) FAIL("gmj_spawn: xyr_dev given without idx_dev");
   if (xy_range < 0 || rot_range < 0) FAIL("gmj_spawn: negative range");
+  if (tries < 1) tries = 1;
+  if (fallback_rot_deg < 0) fallback_rot_deg = 0;
   DeviceGuard dg_(h->device);
   cudaStream_t st = (cudaStream_t)stream;
   int tb = 128, nb = (h->n_envs + tb - 1) / tb;
   uint8_t* ok = ok_dev ? ok_dev : h->spawn_ok;
-  GMJ_FOR_STATE(h, k_spawn<T, QC><<<nb, tb, 0, st>>>((EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->settings, h->objects, h->n_objects, h->n_envs, idx_dev, xyr_dev, mask_dev, xy_range, rot_range, ok, h->err_flag));
+  GMJ_FOR_STATE(h, k_spawn<T, QC><<<nb, tb, 0, st>>>((EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->settings, h->objects, h->n_objects, h->n_envs, idx_dev, xyr_dev, mask_dev, xy_range, rot_range, tries, fallback_xy_mm, fallback_rot_deg, ok, h->err_flag));
   CK(cudaGetLastError());
   return 0;
 }
@@ -704,6 +750,25 @@ int gmj_prof_host(GmjHandle* h, unsigned int* out_host, int clear) {
   return 0;
 }
 #endif
+
+int gmj_event_track_host(GmjHandle* h, int32_t* row_abs_host, float* last_host, float* cum_reward_host) {
+  if (!h || !row_abs_host || !last_host || !cum_reward_host) FAIL("null argument");
+  DeviceGuard dg_(h->device);
+  CK(cudaDeviceSynchronize());
+  constexpr int NE = GBE_COUNT + GLE_COUNT;
+  const size_t n = (size_t)h->n_envs;
+  // scratch counted in doubles: int32[n][NE][2] | float[n][NE] | float[n]
+  const size_t bytes = n * NE * 2 * sizeof(int32_t) + n * NE * sizeof(float) + n * sizeof(float);
+  if (ensure_scratch(h, (bytes + sizeof(double) - 1) / sizeof(double))) return 1;
+  int32_t* ra = (int32_t*)h->scratch; float* la = (float*)(ra + n * NE * 2); float* cr = la + n * NE;
+  int tb = 128, nb = (h->n_envs + tb - 1) / tb;
+  GMJ_FOR_STATE(h, k_event_track<T, QC><<<nb, tb>>>((const EnvState<T, QC>*)h->envs, h->n_envs, ra, la, cr));
+  CK(cudaGetLastError());
+  CK(cudaMemcpy(row_abs_host, ra, n * NE * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(last_host, la, n * NE * sizeof(float), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(cum_reward_host, cr, n * sizeof(float), cudaMemcpyDeviceToHost));
+  return 0;
+}
 
 int gmj_stats(GmjHandle* h, GmjStats* out) {
   if (!h || !out) FAIL("null argument");

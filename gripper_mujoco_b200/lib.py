@@ -28,9 +28,9 @@ PROBE_FIELDS = ["time", "wrist_z", "gauge0", "gauge1", "gauge2", "si_gauge0", "s
 GP = {n: i for i, n in enumerate(PROBE_FIELDS)}
 
 # every symbol include/gmj.h declares (tests check the .so exports exactly these)
-SYMBOLS = ["gmj_create", "gmj_destroy", "gmj_set_settings", "gmj_set_objects", "gmj_reset", "gmj_spawn",
+SYMBOLS = ["gmj_create", "gmj_destroy", "gmj_set_settings", "gmj_set_objects", "gmj_reset", "gmj_reset_done", "gmj_spawn",
            "gmj_step", "gmj_set_action", "gmj_action_step", "gmj_substeps", "gmj_observe", "gmj_n_obs",
-           "gmj_n_actions", "gmj_n_envs", "gmj_get_state_host", "gmj_probe_host", "gmj_probe_host_noalloc", "gmj_stats",
+           "gmj_n_actions", "gmj_n_envs", "gmj_get_state_host", "gmj_probe_host", "gmj_probe_host_noalloc", "gmj_event_track_host", "gmj_stats",
            "gmj_set_welds", "gmj_last_error"]
 
 
@@ -122,7 +122,8 @@ def lib():
     L.gmj_set_settings.argtypes = [vp, C.POINTER(GmjSettings)]
     L.gmj_set_objects.argtypes = [vp, C.POINTER(GmjObject), i32]
     L.gmj_reset.argtypes = [vp, vp, vp]
-    L.gmj_spawn.argtypes = [vp, vp, vp, vp, C.c_double, C.c_double, vp, vp]
+    L.gmj_spawn.argtypes = [vp, vp, vp, vp, C.c_double, C.c_double, i32, i32, i32, vp, vp]
+    L.gmj_reset_done.argtypes = [vp, vp, i32, vp, vp]
     L.gmj_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
     L.gmj_set_action.argtypes = [vp, vp, vp, vp]
     L.gmj_action_step.argtypes = [vp, vp]
@@ -133,6 +134,7 @@ def lib():
     L.gmj_get_state_host.argtypes = [vp, vp, vp]
     L.gmj_probe_host.argtypes = [vp, vp]
     L.gmj_probe_host_noalloc.argtypes = [vp, vp]
+    L.gmj_event_track_host.argtypes = [vp, vp, vp, vp]
     L.gmj_stats.argtypes = [vp, C.POINTER(GmjStats)]
     L.gmj_set_welds.argtypes = [vp, i32, vp]
     _LIB = L

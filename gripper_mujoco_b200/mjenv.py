@@ -135,10 +135,9 @@ class BatchedMjEnv:
         self.mj.default_spawn_params.rotrange = np.pi / 2.0
         # rl/env/MjEnv.py:1216-1244: up to three tries of spawn_into_scene, then the "old method" -- a random pose on the
         # millimetre grid with one of three base angles, placed without a collision test
-        g = self.random_train if not self.test_in_progress else self.random_test
         self.mj.batch.spawn_with_retry(p.object_position_noise_mm * 1e-3, np.pi / 2.0, mask.to(torch.uint8), idx, tries=3,
                                        fallback_xy_mm=int(p.object_position_noise_mm),
-                                       fallback_rot_deg=int(p.object_rotation_noise_deg), generator=g)
+                                       fallback_rot_deg=int(p.object_rotation_noise_deg))
 
     def reset(self, mask=None, hard=None):
         """Reset the envs of `mask` (all if None) and return the observation of EVERY env [n, n_obs]."""

@@ -14,6 +14,7 @@
  *   gmj_set_settings             MjClass::set (mj.set.<field> r/w)      src/bind.cpp:195-204,246-365
  *   gmj_set_objects              luke::get_objects / ObjectHandler::init src/objecthandler.cpp:22-133
  *   gmj_reset                    MjClass::reset                         src/mjclass.cpp:434-486 ; src/bind.cpp:55
+ *   gmj_reset_done               MjEnv.step done / truncation -> MjEnv.reset   rl/env/MjEnv.py:616-637,2222-2263
  *   gmj_spawn                    MjClass::spawn_object(idx,x,y,rot)     src/mjclass.cpp:2323-2420 ; src/bind.cpp:88-95
  *   gmj_step                     set_action + action_step + get_observation + reward + is_done
  *                                src/mjclass.cpp:1483-1698,1700-1959,3000-3049 ; src/bind.cpp:60-66,119-123
@@ -23,6 +24,7 @@
  *   gmj_observe                  get_observation / reward / is_done / get_event_state
  *   gmj_get_state_host           data->qpos / qvel reads (parity dumps)
  *   gmj_probe_host               read_armadillo_gauge / sim_sensors_SI_ latest / calibrate_reset
+ *   gmj_event_track_host         MjClass::get_test_report (TestReport.cnt)  src/mjclass.cpp:3800-3809 ; src/bind.cpp:155
  *   gmj_stats                    (new) solver + stability counters, mirrors BADQACC src/myfunctions.cpp:4233
  */
 #ifndef GMJ_H_
@@ -47,15 +49,24 @@ int gmj_set_objects(GmjHandle* h, const GmjObject* objects_host, int n_objects);
 /* mask_dev: uint8[n_envs] (NULL = all): MjClass::reset of the selected envs. Each env keeps its own episode counter
  * (it keys the counter RNG: draw counter = episode << 12). stream: cudaStream_t as void*. */
 int gmj_reset(GmjHandle* h, const uint8_t* mask_dev, void* stream);
+/* MjEnv.step's end-of-episode rule on the device (rl/env/MjEnv.py:616-637, 2222-2263): reset every env whose done flag
+ * (done_dev uint8[n_envs], as written by gmj_step) is set OR whose episode has reached step_cap action steps
+ * (truncation); mask_out_dev uint8[n_envs] (may be NULL) receives which envs were reset, for the gmj_spawn that follows. */
+int gmj_reset_done(GmjHandle* h, const uint8_t* done_dev, int step_cap, uint8_t* mask_out_dev, void* stream);
 /* idx_dev int32[n_envs], xyr_dev float[n_envs][3] (x, y, z-rotation): spawn_object, placed unconditionally.
  * xyr_dev == NULL: spawn_into_scene -- the reference's search (src/mjclass.cpp:2475-2654): candidate (x, y) on a 2 mm
  * grid within +-xy_range and rotations on a pi/30 grid within +-rot_range, both lists shuffled (counter RNG) and walked
  * pairwise; the first pose whose footprint clears the three fingertip boxes by 1 mm spawns. idx_dev == NULL draws the
  * object per env as well. ok_dev uint8[n_envs] or NULL: 1 where an object was placed, 0 where no candidate was free
  * (spawn_into_scene's `false`: the env has no object, the caller retries / falls back as rl/env/MjEnv.py:1216-1244).
- * mask_dev as above; ok_dev is written for masked-in envs only. */
+ * mask_dev as above; ok_dev is written for masked-in envs only.
+ * tries >= 1: that many spawn_into_scene attempts per env (fresh shuffles each), the loop of MjEnv._spawn_object.
+ * fallback_xy_mm >= 0: an env still without a free pose gets MjEnv's "old method" -- a pose on the millimetre grid
+ * within +-fallback_xy_mm with a base angle of 0 / 60 / 120 degrees +-fallback_rot_deg, no collision test (ok = 2);
+ * fallback_xy_mm < 0: no fallback (ok = 0, the env has no object). */
 int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const uint8_t* mask_dev,
-              double xy_range, double rot_range, uint8_t* ok_dev, void* stream);
+              double xy_range, double rot_range, int tries, int fallback_xy_mm, int fallback_rot_deg,
+              uint8_t* ok_dev, void* stream);
 
 /* fused hot path: actions_dev int32[n_envs] (discrete action index), frac_dev float[n_envs] or NULL.
  * Outputs (any may be NULL): obs_dev float[n_envs][n_obs], reward_dev float[n_envs],
@@ -89,6 +100,10 @@ int gmj_probe_host(GmjHandle* h, double* probe_host);
  * calls on a device share the array: calls that overlap on the GPU race; results equal gmj_probe_host's. */
 #define GMJ_NOALLOC_MAX_ENVS 16384
 int gmj_probe_host_noalloc(GmjHandle* h, double* probe_host);
+/* MjClass::get_test_report / env_.cnt (src/mjclass.cpp:3800-3809, src/mjclass.h:575-647): per env and event (15 binary
+ * then 21 linear, X-macro order) the counters row, abs -> row_abs_host int32[n_envs][36][2], last_value ->
+ * last_host float[n_envs][36], and the cumulative reward -> cum_reward_host float[n_envs]. Host-synchronising. */
+int gmj_event_track_host(GmjHandle* h, int32_t* row_abs_host, float* last_host, float* cum_reward_host);
 int gmj_stats(GmjHandle* h, GmjStats* out);
 /* luke::set_all_constraints / apply_segment_force's weld locking (src/myfunctions.cpp:1157-1170,1642-1727): switch the
  * welds in mask_on (bits 0-2 prismatic, 3-5 revolute, 6 palm) on with their anchors at the current joint values, the

@@ -53,6 +53,7 @@ def lib():
         L.or_forward.argtypes = [C.c_void_p]
         L.or_set_weld.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.or_peek.argtypes = [C.c_void_p, C.c_void_p]
+        L.or_set_fast.argtypes = [C.c_void_p, C.c_int]
         L.or_sample.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.or_sample.restype = C.c_int
         L.or_linear_reward.argtypes = [C.c_float] * 4
@@ -92,6 +93,10 @@ class OracleEnv:
             self.L.or_destroy(self.h)
         except Exception:
             pass
+
+    def set_fast(self, on=True):
+        """Timed-baseline solver (oracle.h: fast_solver): active-set pivoting without the Gauss-Seidel pre-sweeps."""
+        self.L.or_set_fast(self.h, int(bool(on)))
 
     def set_settings(self, s):
         self._s = s

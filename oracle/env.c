@@ -466,11 +466,29 @@ int or_spawn_into_scene(OrEnv* e, const GmjObject* o, double xpos, double ypos, 
   }
   return 0;
 }
+/* MjEnv._spawn_object on one env (rl/env/MjEnv.py:1216-1244): up to `tries` spawn_into_scene attempts, then the "old
+ * method" -- a pose on the millimetre grid within +-fb_xy_mm with a base angle 0 / 60 / 120 degrees +-fb_rot_deg and no
+ * collision test (skipped when fb_xy_mm < 0). Returns 1 (search), 2 (fallback) or 0. Same draws as the device. */
+int or_spawn_retry(OrEnv* e, const GmjObject* o, double xrange, double rotrange, int tries, int fb_xy_mm, int fb_rot_deg) {
+  for (int a = 0; a < tries; a++) {
+    int ok = or_spawn_into_scene(e, o, 0.0, 0.0, 0.0, xrange, xrange, rotrange);
+    if (ok != 0) return ok;
+  }
+  if (fb_xy_mm < 0) return 0;
+  int xm = (int)(or_uniform(e) * (float)(2 * fb_xy_mm + 1)); if (xm > 2 * fb_xy_mm) xm = 2 * fb_xy_mm;
+  int ym = (int)(or_uniform(e) * (float)(2 * fb_xy_mm + 1)); if (ym > 2 * fb_xy_mm) ym = 2 * fb_xy_mm;
+  int an = (int)(or_uniform(e) * (float)(2 * fb_rot_deg + 1)); if (an > 2 * fb_rot_deg) an = 2 * fb_rot_deg;
+  int bi = (int)(or_uniform(e) * 3.0f); if (bi > 2) bi = 2;
+  or_spawn(e, o, (xm - fb_xy_mm) * 1e-3, (ym - fb_xy_mm) * 1e-3, (60 * bi + an - fb_rot_deg) * (M_PI / 180.0));
+  return 2;
+}
 /* object index draw of the batched env (device: same draw, before the pose search) */
 int or_draw_object(OrEnv* e, int n_objects) {
   int oi = (int)(or_uniform(e) * n_objects); if (oi >= n_objects) oi = n_objects - 1;
   return oi;
 }
+
+void or_set_fast(OrEnv* e, int on) { e->fast_solver = on; }
 
 void or_set_script(OrEnv* e, const double* rows, int nrows) {
   e->script = rows; e->script_rows = nrows; e->script_cursor = 0;

@@ -104,6 +104,10 @@ typedef struct OrEnv {
    * rows oracle/ref_tail_shim.cpp feeds to the reference's own compiled MjClass */
   const double* script; int script_rows, script_cursor;
   double script_cur[OR_SCRIPT_ROWLEN];
+  /* 1: the timed CPU baseline's solver -- straight to the active-set pivoting solve from the warm start, without the
+   * Gauss-Seidel sweeps to 1e-13 the parity oracle runs first (same unique solution; bench.py's CPU arms use it so the
+   * baseline is not handicapped by the checker's belt and braces) */
+  int fast_solver;
 } OrEnv;
 
 /* ---- gripper motor space (src/gripper.h, src/gripper.cpp) */
@@ -150,7 +154,9 @@ void or_set_weld(OrEnv* e, int id, int on);
 int or_struct_size(void);
 int or_spawn_ok(const OrEnv* e, double x, double y, double rot, const double* bbox3);
 int or_spawn_into_scene(OrEnv* e, const GmjObject* o, double x, double y, double zrot, double xrange, double yrange, double rotrange);
+int or_spawn_retry(OrEnv* e, const GmjObject* o, double xrange, double rotrange, int tries, int fb_xy_mm, int fb_rot_deg);
 int or_draw_object(OrEnv* e, int n_objects);
+void or_set_fast(OrEnv* e, int on);
 void or_set_script(OrEnv* e, const double* rows, int nrows);
 
 #ifdef __cplusplus

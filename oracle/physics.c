@@ -162,6 +162,45 @@ static void chol_solve(const double* L, int n, double* x) {
   for (int i = n - 1; i >= 0; i--) { double s = x[i]; for (int k = i + 1; k < n; k++) s -= L[k * n + i] * x[k]; x[i] = s / L[i * n + i]; }
 }
 
+/* ---- timed-baseline path (OrEnv::fast_solver): the same factorisations in a FILL-FREE ordering. With the dofs ordered
+ * fingers, palm, base, object the mass matrix is block-arrow (finger blocks couple only through the base row), so row
+ * i of its Cholesky factor starts at first[i] -- a skyline factorisation does the tree-sparse L D L^T work MuJoCo does,
+ * instead of dense nv^3 / 3. Same arithmetic on the non-zero entries; the checker path keeps the dense routines. */
+static int chol_sky(double* A, int n, const int* first) {
+  for (int j = 0; j < n; j++) {
+    double d = A[j * n + j];
+    for (int k = first[j]; k < j; k++) d -= A[j * n + k] * A[j * n + k];
+    if (!(d > 0)) return 0;
+    d = sqrt(d); A[j * n + j] = d;
+    for (int i = j + 1; i < n; i++) {
+      if (first[i] > j) { A[i * n + j] = 0; continue; }
+      double s = A[i * n + j];
+      for (int k = first[i] > first[j] ? first[i] : first[j]; k < j; k++) s -= A[i * n + k] * A[j * n + k];
+      A[i * n + j] = s / d;
+    }
+  }
+  return 1;
+}
+static void chol_solve_sky(const double* L, int n, const int* first, const int* perm, double* v) {
+  double x[OR_MAXV];
+  for (int i = 0; i < n; i++) x[i] = v[perm[i]];
+  int i0 = 0; while (i0 < n && x[i0] == 0.0) i0++;               /* leading zeros of the right-hand side stay zero */
+  for (int i = i0; i < n; i++) { double s = x[i]; for (int k = first[i] > i0 ? first[i] : i0; k < i; k++) s -= L[i * n + k] * x[k]; x[i] = s / L[i * n + i]; }
+  for (int i = n - 1; i >= 0; i--) { x[i] /= L[i * n + i]; const double xi = x[i]; for (int k = first[i]; k < i; k++) x[k] -= L[i * n + k] * xi; }
+  for (int i = 0; i < n; i++) v[perm[i]] = x[i];
+}
+static void sky_setup(const OrEnv* e, const double* M, double* Mp, int* perm, int* first) {
+  int nv = e->nv, B = e->B, n = 0;
+  for (int i = 1; i < B; i++) perm[n++] = i;                    /* fingers (prismatic, revolute, segments) x 3, palm */
+  perm[n++] = 0;                                                 /* base last among the gripper dofs: no fill-in */
+  for (int i = B; i < nv; i++) perm[n++] = i;                   /* object */
+  for (int i = 0; i < nv; i++) {
+    first[i] = i;
+    for (int j = 0; j < nv; j++) Mp[i * nv + j] = M[perm[i] * nv + perm[j]];
+    for (int j = 0; j < i; j++) if (Mp[i * nv + j] != 0.0) { first[i] = j; break; }
+  }
+}
+
 /* translational + rotational Jacobian of body b at world point p: rows x,y,z (3 x nv each) */
 static void jac_point(const OrEnv* e, int b, const double p[3], double* Jp, double* Jr) {
   const GmjModel* m = &e->m;
@@ -302,10 +341,15 @@ void or_physics_step(OrEnv* e) {
       for (int j = 0; j < nv; j++) qfrc[j] += Jp1[j] * fv[0] + Jp1[nv + j] * fv[1] + Jp1[2 * nv + j] * fv[2];
     }
   }
-  memcpy(L, M, sizeof(double) * nv * nv);
-  if (!chol(L, nv)) { e->unstable = 1; return; }
+  static int perm[OR_MAXV], first[OR_MAXV];
+  const int sky = e->fast_solver;
+  if (sky) { sky_setup(e, M, L, perm, first); if (!chol_sky(L, nv, first)) { e->unstable = 1; return; } }
+  else {
+    memcpy(L, M, sizeof(double) * nv * nv);
+    if (!chol(L, nv)) { e->unstable = 1; return; }
+  }
   memcpy(qacc_s, qfrc, sizeof(double) * nv);
-  chol_solve(L, nv, qacc_s);
+  if (sky) chol_solve_sky(L, nv, first, perm, qacc_s); else chol_solve(L, nv, qacc_s);
 
   /* ---- constraint rows */
   int nr = 0;
@@ -364,7 +408,10 @@ void or_physics_step(OrEnv* e) {
   e->nrow = nr;
 
   /* ---- A = J M^-1 J^T, regulariser R, reference acceleration */
-  for (int r = 0; r < nr; r++) { memcpy(Bm[r], J[r], sizeof(double) * nv); chol_solve(L, nv, Bm[r]); }
+  for (int r = 0; r < nr; r++) {
+    memcpy(Bm[r], J[r], sizeof(double) * nv);
+    if (sky) chol_solve_sky(L, nv, first, perm, Bm[r]); else chol_solve(L, nv, Bm[r]);
+  }
   for (int r = 0; r < nr; r++) for (int c = r; c < nr; c++) {
     double s = 0;
     for (int j = 0; j < nv; j++) s += J[r][j] * Bm[c][j];
@@ -395,7 +442,7 @@ void or_physics_step(OrEnv* e) {
   /* ---- dual QP by projected Gauss-Seidel, warm-started, to convergence */
   if (nr == e->nrow_prev) memcpy(fr, e->efc_force_prev, sizeof(double) * nr); else memset(fr, 0, sizeof(double) * nr);
   int it = 0;
-  for (; it < 4000 && nr > 0; it++) {
+  for (; it < 4000 && nr > 0 && !e->fast_solver; it++) {
     double change = 0, scale = 0;
     for (int r = 0; r < nr; r++) {
       double res = bvec[r] + Rr[r] * fr[r];
@@ -434,8 +481,14 @@ void or_physics_step(OrEnv* e) {
 
   /* ---- Euler, joint damping implicit: (M + dt D) a = qfrc_smooth + qfrc_constraint */
   for (int i = 0; i < B; i++) M[i * nv + i] += dt * m->damping[i];
-  if (!chol(M, nv)) { e->unstable = 1; return; }
-  chol_solve(M, nv, qfrc);
+  if (sky) {
+    sky_setup(e, M, L, perm, first);
+    if (!chol_sky(L, nv, first)) { e->unstable = 1; return; }
+    chol_solve_sky(L, nv, first, perm, qfrc);
+  } else {
+    if (!chol(M, nv)) { e->unstable = 1; return; }
+    chol_solve(M, nv, qfrc);
+  }
   for (int j = 0; j < nv; j++) e->qvel[j] += dt * qfrc[j];
   for (int i = 0; i < B; i++) e->qpos[i] += dt * e->qvel[i];
   if (e->has_object) {

@@ -24,7 +24,9 @@ def _init(root, n_segments, settings_bytes, seed_base):
     st = GmjSettings.from_buffer_copy(settings_bytes)
     mdl = build_model(GripperParams(num_segments=n_segments))
     rank = mp.current_process()._identity[0] if mp.current_process()._identity else 0
-    _W.update(env=OracleEnv(mdl.to_struct(), st), objs=build_object_set(), rng=np.random.default_rng(seed_base + rank),
+    env = OracleEnv(mdl.to_struct(), st)
+    env.set_fast(True)            # timed baseline: direct active-set solve (oracle.h fast_solver), same results to 1e-9
+    _W.update(env=env, objs=build_object_set(), rng=np.random.default_rng(seed_base + rank),
               rank=rank, episode=0, steps_in_ep=0, seed=int(st.general[3]), n_actions=None, need_reset=True)
 
 

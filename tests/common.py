@@ -111,3 +111,57 @@ class OracleBatch:
 
     def qvel(self):
         return np.stack([e.qvel() for e in self.envs])
+
+
+# ------------------------------------------------------------------ oracle trajectories on all host cores
+_RW: dict = {}
+
+
+def _roll_init(root, n_segments, settings_bytes):
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    from gripper_mujoco_b200.settings import GmjSettings
+    st = GmjSettings.from_buffer_copy(settings_bytes)
+    mdl = build_model(GripperParams(num_segments=n_segments))
+    _RW.update(ms=mdl.to_struct(), ss=st, objs=build_object_set(), seed=int(st.general[3]), B=mdl.B)
+
+
+def _roll_chunk(args):
+    """One oracle env per entry: reset(seed, env id, episode) -> spawn -> T x (set_action, action_step, observation,
+    is_done, reward, event_state); per step outputs + per step qpos / qvel."""
+    env_ids, episode, obj_idx, xyr, actions, frac, search = args
+    w = _RW
+    out = []
+    for k, eid in enumerate(env_ids):
+        e = OracleEnv(w["ms"], w["ss"])
+        e.reset(w["seed"], int(eid), int(episode))
+        if search is not None:          # MjEnv's spawn policy with the env's own draws (gmj_spawn with tries / fallback)
+            e.L.or_spawn_retry.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int]
+            e.L.or_spawn_retry(e.h, C.byref(w["objs"][int(obj_idx[k])].obj), *search)
+        elif obj_idx[k] >= 0:
+            e.spawn(w["objs"][int(obj_idx[k])].obj, float(xyr[k, 0]), float(xyr[k, 1]), float(xyr[k, 2]))
+        obs, rew, done, ev, qp, qv = [], [], [], [], [], []
+        for t in range(actions.shape[0]):
+            rc = e.set_action(int(actions[t, k])) if frac is None else e.set_action(int(actions[t, k]), float(frac[t, k]))
+            assert rc == 0
+            e.action_step()
+            obs.append(e.observation()); done.append(e.is_done()); rew.append(np.float32(e.reward())); ev.append(e.event_state())
+            qp.append(e.qpos()); qv.append(e.qvel())
+        out.append((np.stack(obs), np.array(rew, dtype=np.float32), np.array(done), np.stack(ev), np.stack(qp), np.stack(qv)))
+    return out
+
+
+def oracle_rollout(N, st, env_ids, episode, obj_idx, xyr, actions, frac=None, cores=None, search=None):
+    """Oracle trajectories of many independent envs, spread over the host cores (one process per core).
+    actions: int [T, n]. Returns dict of arrays with a leading [T, n] (obs, reward, done, events, qpos, qvel)."""
+    import multiprocessing as mp
+    cores = cores or len(os.sched_getaffinity(0))
+    env_ids = np.asarray(env_ids); n = len(env_ids)
+    chunks = np.array_split(np.arange(n), min(n, cores * 4))
+    ctx = mp.get_context("spawn")
+    with ctx.Pool(cores, initializer=_roll_init, initargs=(ROOT, N, bytes(st.pack()))) as pool:
+        res = pool.map(_roll_chunk, [(env_ids[c], episode, np.asarray(obj_idx)[c], np.asarray(xyr)[c], np.asarray(actions)[:, c],
+                                      None if frac is None else np.asarray(frac)[:, c], search) for c in chunks], chunksize=1)
+    flat = [r for ch in res for r in ch]
+    keys = ("obs", "reward", "done", "events", "qpos", "qvel")
+    return {k: np.stack([f[i] for f in flat], axis=1) for i, k in enumerate(keys)}

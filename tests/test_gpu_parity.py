@@ -212,6 +212,23 @@ def test_spawn_search_matches_oracle():
         assert dq < 2e-7, (xr, rr, dq)       # quaternion: device vs libm sin / cos of -rot / 2
         fails += int(n - ok_o.sum())
     assert fails > 0                           # envs whose object fits nowhere are really exercised
+    # MjEnv's policy in one launch: three attempts, then the unconditional fallback pose
+    L.or_spawn_retry.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int]
+    gb.reset()
+    ok_g = gb.spawn_with_retry(0.01, float(np.pi / 2), None, None, tries=3, fallback_xy_mm=10, fallback_rot_deg=5).cpu().numpy().astype(int)
+    qg, _ = gb.state()
+    oi_g = gb.probe_field("obj_index").astype(int)
+    ep = int(gb.probe_field("episode")[0])
+    ok_o, oi_o, q_o = np.zeros(n, int), np.zeros(n, int), np.zeros((n, 7))
+    for i in range(n):
+        e = OracleEnv(ms, ss)
+        e.reset(int(st.random_seed), i, ep)
+        oi = L.or_draw_object(e.h, len(objs))
+        ok_o[i] = L.or_spawn_retry(e.h, C.byref(objs[oi].obj), 0.01, float(np.pi / 2), 3, 10, 5)
+        oi_o[i] = oi; q_o[i] = e.qpos()[B:B + 7]
+    assert np.array_equal(ok_g, ok_o) and np.array_equal(oi_g, oi_o)
+    assert (ok_o >= 1).all() and (ok_o == 2).any()            # everybody has an object; the fallback was exercised
+    assert np.abs(qg[:, B:B + 3] - q_o[:, :3]).max() < 1e-7 and np.abs(qg[:, B + 3:B + 7] - q_o[:, 3:]).max() < 2e-7
     gb.close()
 
 

@@ -209,3 +209,28 @@ def test_oracle_cantilever_matches_the_stiffness_derivation(N, dt):
         th = q[3 + f * (N + 2): 3 + f * (N + 2) + N]
         d = float((ell * np.sin(np.cumsum(th))).sum())
         assert abs(d / pred - 1) < 0.035, (f, d, pred)
+
+
+def test_oracle_timed_baseline_mode_equals_the_checker():
+    """bench.py's CPU arms run the oracle with fast_solver = 1 (oracle.h): straight to the active-set pivoting solve,
+    skyline (tree-sparse) Cholesky in a fill-free dof order. Same model, same unique solution: trajectories of
+    contact-rich random rollouts must agree with the checker path (Gauss-Seidel to 1e-13 + polish, dense
+    factorisations) to rounding."""
+    from common import make_pair, objects
+    from oracle.binding import OracleEnv
+    mdl, st = make_pair(5, 7.02e-3, steps_per_action=29, noise=True)
+    out = []
+    for fast in (0, 1):
+        e = OracleEnv(mdl.to_struct(), st.pack()); e.set_fast(fast)
+        rng = np.random.default_rng(0); qs, ev = [], []
+        for ep in range(3):
+            e.reset(1234, 0, ep + 1); e.spawn(objects()[int(rng.integers(0, 1750))].obj, 0.004, -0.002, 0.3)
+            for t in range(24):
+                e.set_action(int(rng.integers(0, 14)) if t < 16 else 1); e.action_step()
+                qs.append(e.qpos().copy()); ev.append(e.event_state())
+                if e.is_done():
+                    break
+        out.append((np.stack(qs), np.stack(ev), e.peek().contacts))
+    assert out[0][2] > 1000                                     # contacts were simulated
+    assert np.abs(out[0][0] - out[1][0]).max() < 1e-10
+    assert np.array_equal(out[0][1][:, :15], out[1][1][:, :15])

@@ -56,6 +56,7 @@ __global__ void k_reset(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const Dev
   g_reset(e.tend); g_reset(e.tnext);
   for (int i = 0; i < B; i++) e.qpos[i] = M.qpos0[i];
   // parked object (dead collision group): not simulated
+  e.obj_xy[0] = 0; e.obj_xy[1] = 2;
   e.qpos[OQ] = 0; e.qpos[OQ + 1] = 2; e.qpos[OQ + 2] = 1; e.qpos[OQ + 3] = 0; e.qpos[OQ + 4] = 0; e.qpos[OQ + 5] = 0; e.qpos[OQ + 6] = 1;
   // weld anchors from the keyframe pose (xpos/xmat are stale when set_all_constraints runs), then
   // the stored equilibrium of base + motor joints (calibrate_reset)
@@ -127,37 +128,60 @@ __device__ inline int box2d_overlap(const double* a, const double* o, double min
 // (oracle/env.c or_spawn_into_scene draws the same numbers).
 #define GMJ_SPAWN_MAXXY 1024
 #define GMJ_SPAWN_MAXROT 128
-template <typename T, int QC>
-__device__ inline void fy_shuffle(EnvState<T, QC>& e, const DevSettings& S, unsigned short* a, int n) {
-  for (int i = n - 1; i >= 1; i--) {
-    int j = (int)(dev_uniform(e, S) * (float)(i + 1)); if (j > i) j = i;
-    unsigned short t = a[i]; a[i] = a[j]; a[j] = t;
+// One WARP per env: the Fisher-Yates draws (counter RNG, draw k = philox(ctr + k)) are formed by all lanes, the swaps
+// applied in order by lane 0, and the candidate walk tests 32 poses at a time (first passing index wins, so the result
+// equals the serial walk). One thread per env made the unlucky env (large object, 3 x 121 FP64 SAT tests) a ~1 ms
+// serial tail on every bench step.
+#define GMJ_SPAWN_WPB 4
+__device__ __forceinline__ float spawn_draw(uint32_t ctr, uint32_t env_id, uint64_t seed) {
+  uint32_t x = philox_first(ctr, env_id, 0, 0, (uint32_t)seed, (uint32_t)(seed >> 32));
+  return (float)(x >> 8) * (1.0f / 16777216.0f);
+}
+__device__ inline void fy_shuffle_warp(uint32_t& ctr, uint32_t env_id, uint64_t seed, unsigned short* a, unsigned short* js, int n, int lane) {
+  for (int i = lane; i < n; i += 32) a[i] = (unsigned short)i;
+  for (int k = lane; k < n - 1; k += 32) {              // draw k belongs to i = n - 1 - k
+    const int i = n - 1 - k;
+    int j = (int)(spawn_draw(ctr + k, env_id, seed) * (float)(i + 1)); if (j > i) j = i;
+    js[i] = (unsigned short)j;
   }
+  ctr += n - 1;
+  __syncwarp();
+  if (lane == 0) for (int i = n - 1; i >= 1; i--) { const int j = js[i]; unsigned short t = a[i]; a[i] = a[j]; a[j] = t; }
+  __syncwarp();
 }
 template <typename T, int QC>
-__global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const DevSettings* Sp, const GmjObject* objects, int n_objects,
-                        int n_envs, const int32_t* idx, const float* xyr, const uint8_t* mask, double xy_range, double rot_range,
-                        int tries_max, int fb_xy_mm, int fb_rot_deg, uint8_t* ok_out, int* err_flag) {
-  int env = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(32 * GMJ_SPAWN_WPB)
+k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const DevSettings* Sp, const GmjObject* objects, int n_objects,
+        int n_envs, const int32_t* idx, const float* xyr, const uint8_t* mask, double xy_range, double rot_range,
+        int tries_max, int fb_xy_mm, int fb_rot_deg, uint8_t* ok_out, int* err_flag) {
+  __shared__ unsigned short s_pxy[GMJ_SPAWN_WPB][GMJ_SPAWN_MAXXY], s_js[GMJ_SPAWN_WPB][GMJ_SPAWN_MAXXY], s_pr[GMJ_SPAWN_WPB][GMJ_SPAWN_MAXROT];
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int env = blockIdx.x * GMJ_SPAWN_WPB + wib;
   if (env >= n_envs) return;
   if (mask && !mask[env]) return;
   constexpr int OQ = QC - 8;
   EnvState<T, QC>& e = envs[env];
   const DevSettings& S = *Sp; const DevModelS<T>& M = *Mp;
-  int oi; double x = 0, y = 0, rot = 0;
-  ok_out[env] = 0;
+  const uint64_t seed = (uint64_t)S.s.general[GS_random_seed];
+  const uint32_t env_id = e.env_id;
+  uint32_t ctr = e.rng_ctr;                      // every lane keeps the same counter; lane 0 stores it at the end
+  int oi = 0; double x = 0, y = 0, rot = 0;
+  int found = 0;
   if (idx) {
     oi = idx[env];
-    if (oi < 0 || oi >= n_objects) { if (err_flag) atomicExch(err_flag, 2); return; }
+    if (oi < 0 || oi >= n_objects) { if (lane == 0) { ok_out[env] = 0; if (err_flag) atomicExch(err_flag, 2); } return; }
   }
-  if (idx && xyr) { x = xyr[3 * env]; y = xyr[3 * env + 1]; rot = xyr[3 * env + 2]; ok_out[env] = 1; }
+  if (idx && xyr) { x = xyr[3 * env]; y = xyr[3 * env + 1]; rot = xyr[3 * env + 2]; found = 1; }
   else {
-    if (!idx) { oi = (int)(dev_uniform(e, S) * n_objects); if (oi >= n_objects) oi = n_objects - 1; }
+    if (!idx) { oi = (int)(spawn_draw(ctr++, env_id, seed) * n_objects); if (oi >= n_objects) oi = n_objects - 1; }
     const GmjObject& ob = objects[oi];
     const double inc = 2e-3, rinc = 3.14159265358979323846 / 30.0, gap = 1e-3;
     const int num_x = (int)((2 * xy_range) / inc) + 1, num_y = num_x, num_r = (int)((2 * rot_range) / rinc) + 1;
     const int nxy = num_x * num_y;
-    if (nxy > GMJ_SPAWN_MAXXY || num_r > GMJ_SPAWN_MAXROT) { if (err_flag) atomicExch(err_flag, 3); return; }
+    if (nxy > GMJ_SPAWN_MAXXY || num_r > GMJ_SPAWN_MAXROT) {
+      if (lane == 0) { ok_out[env] = 0; e.rng_ctr = ctr; if (err_flag) atomicExch(err_flag, 3); }
+      return;
+    }
     double tips[3][8];
     {
       DevGripper home; g_reset(home);
@@ -169,42 +193,51 @@ __global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const Dev
         box2d_init(tips[i], px, py, (double)M.finger_width, (double)M.hook_length, -ang);
       }
     }
-    unsigned short pxy[GMJ_SPAWN_MAXXY], pr[GMJ_SPAWN_MAXROT];
-    int found = 0;
+    unsigned short* pxy = s_pxy[wib]; unsigned short* pr = s_pr[wib]; unsigned short* js = s_js[wib];
+    const int tries = nxy > num_r ? nxy : num_r;
     // MjEnv._spawn_object: up to tries_max calls of spawn_into_scene (each with fresh shuffles), rl/env/MjEnv.py:1216-1227
     for (int attempt = 0; attempt < tries_max && !found; attempt++) {
-    for (int i = 0; i < nxy; i++) pxy[i] = (unsigned short)i;
-    for (int i = 0; i < num_r; i++) pr[i] = (unsigned short)i;
-    if (nxy > 1) fy_shuffle(e, S, pxy, nxy);
-    if (num_r > 1) fy_shuffle(e, S, pr, num_r);
-    const int tries = nxy > num_r ? nxy : num_r;
-    for (int i = 0; i < tries && !found; i++) {
-      const int k = pxy[i % nxy], ix = k / num_y, iy = k % num_y, ir = pr[i % num_r];
-      x = num_x > 1 ? -xy_range + ix * inc + 0.0 : 0.0;
-      y = num_y > 1 ? -xy_range + iy * inc + 0.0 : 0.0;
-      rot = num_r > 1 ? -rot_range + ir * rinc + 0.0 : 0.0;
-      double ours[8];
-      box2d_init(ours, x, y, ob.bbox[0], ob.bbox[1], rot);
-      int ok = 1;
-      for (int c = 0; c < 4; c++) if (ours[c] < -100 || ours[c] > 100 || ours[4 + c] < -100 || ours[4 + c] > 100) ok = 0;
-      for (int t = 0; t < 3 && ok; t++) if (box2d_overlap(ours, tips[t], gap)) ok = 0;
-      found = ok;
-    }
+      if (nxy > 1) fy_shuffle_warp(ctr, env_id, seed, pxy, js, nxy, lane); else { if (lane == 0) pxy[0] = 0; __syncwarp(); }
+      if (num_r > 1) fy_shuffle_warp(ctr, env_id, seed, pr, js, num_r, lane); else { if (lane == 0) pr[0] = 0; __syncwarp(); }
+      for (int base = 0; base < tries && !found; base += 32) {
+        const int i = base + lane;
+        int ok = 0;
+        if (i < tries) {
+          const int k = pxy[i % nxy], ix = k / num_y, iy = k % num_y, ir = pr[i % num_r];
+          x = num_x > 1 ? -xy_range + ix * inc + 0.0 : 0.0;
+          y = num_y > 1 ? -xy_range + iy * inc + 0.0 : 0.0;
+          rot = num_r > 1 ? -rot_range + ir * rinc + 0.0 : 0.0;
+          double ours[8];
+          box2d_init(ours, x, y, ob.bbox[0], ob.bbox[1], rot);
+          ok = 1;
+          for (int c = 0; c < 4; c++) if (ours[c] < -100 || ours[c] > 100 || ours[4 + c] < -100 || ours[4 + c] > 100) ok = 0;
+          for (int t = 0; t < 3 && ok; t++) if (box2d_overlap(ours, tips[t], gap)) ok = 0;
+        }
+        const unsigned hit = __ballot_sync(0xffffffffu, ok);
+        if (hit) {
+          const int src = __ffs(hit) - 1;
+          x = __shfl_sync(0xffffffffu, x, src); y = __shfl_sync(0xffffffffu, y, src); rot = __shfl_sync(0xffffffffu, rot, src);
+          found = 1;
+        }
+      }
+      __syncwarp();
     }
     if (!found) {
-      if (fb_xy_mm < 0) return;
+      if (fb_xy_mm < 0) { if (lane == 0) { ok_out[env] = 0; e.rng_ctr = ctr; } return; }
       // "old method" of MjEnv._spawn_object (rl/env/MjEnv.py:1229-1244): a pose on the millimetre grid with one of the
       // base angles 0 / 60 / 120 degrees +- fb_rot_deg, placed without a collision test
-      int xm = (int)(dev_uniform(e, S) * (float)(2 * fb_xy_mm + 1)); if (xm > 2 * fb_xy_mm) xm = 2 * fb_xy_mm;
-      int ym = (int)(dev_uniform(e, S) * (float)(2 * fb_xy_mm + 1)); if (ym > 2 * fb_xy_mm) ym = 2 * fb_xy_mm;
-      int an = (int)(dev_uniform(e, S) * (float)(2 * fb_rot_deg + 1)); if (an > 2 * fb_rot_deg) an = 2 * fb_rot_deg;
-      int bi = (int)(dev_uniform(e, S) * 3.0f); if (bi > 2) bi = 2;
+      int xm = (int)(spawn_draw(ctr++, env_id, seed) * (float)(2 * fb_xy_mm + 1)); if (xm > 2 * fb_xy_mm) xm = 2 * fb_xy_mm;
+      int ym = (int)(spawn_draw(ctr++, env_id, seed) * (float)(2 * fb_xy_mm + 1)); if (ym > 2 * fb_xy_mm) ym = 2 * fb_xy_mm;
+      int an = (int)(spawn_draw(ctr++, env_id, seed) * (float)(2 * fb_rot_deg + 1)); if (an > 2 * fb_rot_deg) an = 2 * fb_rot_deg;
+      int bi = (int)(spawn_draw(ctr++, env_id, seed) * 3.0f); if (bi > 2) bi = 2;
       x = (xm - fb_xy_mm) * 1e-3; y = (ym - fb_xy_mm) * 1e-3;
       rot = (60 * bi + an - fb_rot_deg) * (3.14159265358979323846 / 180.0);
       found = 2;
     }
-    ok_out[env] = (uint8_t)found;
   }
+  if (lane != 0) return;
+  ok_out[env] = (uint8_t)found;
+  e.rng_ctr = ctr;
   const GmjObject& ob = objects[oi];
   e.obj[0] = (T)ob.type; e.obj[1] = (T)ob.size[0]; e.obj[2] = (T)ob.size[1]; e.obj[3] = (T)ob.size[2]; e.obj[4] = (T)ob.round;
   e.obj[5] = (T)ob.quat[0]; e.obj[6] = (T)ob.quat[1]; e.obj[7] = (T)ob.quat[2]; e.obj[8] = (T)ob.quat[3];
@@ -213,6 +246,7 @@ __global__ void k_spawn(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const Dev
   e.obj_index = oi; e.has_object = 1;
   double z = ob.z_rest + 1e-6;
   e.qpos[OQ] = (T)x; e.qpos[OQ + 1] = (T)y; e.qpos[OQ + 2] = (T)z;
+  e.obj_xy[0] = x; e.obj_xy[1] = y;
   e.qpos[OQ + 3] = (T)sin(-rot / 2.0); e.qpos[OQ + 4] = 0; e.qpos[OQ + 5] = 0; e.qpos[OQ + 6] = (T)cos(-rot / 2.0);
   for (int k = 0; k < 6; k++) e.qvel[OQ + k] = 0;
   e.start_z = (double)(T)z;
@@ -607,7 +641,7 @@ int gmj_spawn(GmjHandle* h, const int32_t* idx_dev, const float* xyr_dev, const 
   if (fallback_rot_deg < 0) fallback_rot_deg = 0;
   DeviceGuard dg_(h->device);
   cudaStream_t st = (cudaStream_t)stream;
-  int tb = 128, nb = (h->n_envs + tb - 1) / tb;
+  int tb = 32 * GMJ_SPAWN_WPB, nb = (h->n_envs + GMJ_SPAWN_WPB - 1) / GMJ_SPAWN_WPB;
   uint8_t* ok = ok_dev ? ok_dev : h->spawn_ok;
   GMJ_FOR_STATE(h, k_spawn<T, QC><<<nb, tb, 0, st>>>((EnvState<T, QC>*)h->envs, (const DevModelS<T>*)h->model_s, h->settings, h->objects, h->n_objects, h->n_envs, idx_dev, xyr_dev, mask_dev, xy_range, rot_range, tries, fallback_xy_mm, fallback_rot_deg, ok, h->err_flag));
   CK(cudaGetLastError());

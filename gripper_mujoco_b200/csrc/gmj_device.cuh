@@ -36,6 +36,8 @@ struct EnvState {
   DevGripper tend, tnext;     // target_.end / target_.next
   double base_x, base_y, base_z, base_yaw;
   double start_z;
+  double obj_xy[2];           // object x, y integrated in double beside the FP32 qpos (events compare it with thresholds the
+                              // spawn grid puts objects exactly ON: within_XY_distance, src/mjclass.cpp:1237)
   float win[GMJ_NSTREAM][GMJ_WIN];
   int win_i[GMJ_NSTREAM];
   float si_latest[5];         // latest SI readings: gauge1-3, palm, wristZ

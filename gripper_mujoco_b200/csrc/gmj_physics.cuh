@@ -1001,6 +1001,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
       vo = vo + mk<T>(ao[0], ao[1], ao[2]) * dt; wo = wo + mk<T>(ao[3], ao[4], ao[5]) * dt;
       e.qvel[32] = vo.x; e.qvel[33] = vo.y; e.qvel[34] = vo.z; e.qvel[35] = wo.x; e.qvel[36] = wo.y; e.qvel[37] = wo.z;
       e.qpos[32] += dt * vo.x; e.qpos[33] += dt * vo.y; e.qpos[34] += dt * vo.z;
+      e.obj_xy[0] += dtd * (double)vo.x; e.obj_xy[1] += dtd * (double)vo.y;
       T ang = sqrtT<T>(dot(wo, wo)) * dt;
       T a0 = e.qpos[35], a1 = e.qpos[36], a2 = e.qpos[37], a3 = e.qpos[38];
       if (ang > 0) {

@@ -759,6 +759,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
         vo = vo + mk<T>(ao[0], ao[1], ao[2]) * dt; wo = wo + mk<T>(ao[3], ao[4], ao[5]) * dt;
         e.qvel[OQ] = vo.x; e.qvel[OQ + 1] = vo.y; e.qvel[OQ + 2] = vo.z; e.qvel[OQ + 3] = wo.x; e.qvel[OQ + 4] = wo.y; e.qvel[OQ + 5] = wo.z;
         e.qpos[OQ] += dt * vo.x; e.qpos[OQ + 1] += dt * vo.y; e.qpos[OQ + 2] += dt * vo.z;
+        e.obj_xy[0] += dtd * (double)vo.x; e.obj_xy[1] += dtd * (double)vo.y;
         T ang = sqrtT<T>(dot(wo, wo)) * dt;
         T a0 = e.qpos[OQ + 3], a1 = e.qpos[OQ + 4], a2 = e.qpos[OQ + 5], a3 = e.qpos[OQ + 6];
         if (ang > 0) {

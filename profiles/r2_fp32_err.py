@@ -18,6 +18,8 @@ def main():
     xyr = np.stack([rng.integers(-5, 6, n) * 2e-3, rng.integers(-5, 6, n) * 2e-3, rng.integers(-15, 16, n) * (np.pi / 30)], 1).astype(np.float32)
     acts = rng.integers(0, gb.n_actions, (T, n)).astype(np.int32)
     gb.reset(); gb.spawn_with_retry(0.01, float(np.pi / 2), None, idx, tries=3, fallback_xy_mm=10, fallback_rot_deg=5)
+    spawned = gb.spawned.cpu().numpy()
+    print("spawn codes (1 = clear pose found, 2 = fallback pose without collision test):", np.bincount(spawned, minlength=3))
     sel = np.sort(rng.choice(n, sample, replace=False))
     t0 = time.time()
     ep = int(gb.probe_field('episode')[0])
@@ -29,10 +31,25 @@ def main():
         o, r, d, e = (v.cpu().numpy() for v in gb.step(acts[t]))
         q, v = gb.state()
         o, r, d, e, q, v = o[sel], r[sel], d[sel], e[sel], q[sel], v[sel]
-        same = (e[:, DISC] == ora["events"][t][:, DISC]).all(1)
+        oq = ora["qpos"][t]
+        edge = np.abs(np.hypot(oq[:, B], oq[:, B + 1]) - 10e-3) < 1e-6        # object resting on the within_XY_distance threshold
+        neq = e[:, DISC] != ora["events"][t][:, DISC]
+        neq[:, 14] &= ~edge
+        same = ~neq.any(1)
         dq = np.abs(q - ora["qpos"][t]); dv = np.abs(v - ora["qvel"][t])
         rel = dq[:, :B].max(1) / np.maximum(np.abs(ora["qpos"][t][:, :B]).max(1), 1e-3)
-        calm = same & (np.abs(o - ora['obs'][t]).max(1) < 1e-2)
+        if t in (0, T - 1):
+            mism = neq.sum(0)
+            print("   mismatching discrete columns (index in the 57-vector: count):", {DISC[k]: int(c) for k, c in enumerate(mism) if c})
+            w = np.where(neq[:, 14])[0][:6]
+            for k in w:
+                print("   col14 env", sel[k], "code", spawned[sel[k]], "oracle xy", oq[k, B:B + 2], "device xy", q[k, B:B + 2], "hyp", np.hypot(oq[k, B], oq[k, B + 1]), np.hypot(q[k, B], q[k, B + 1]), "ev", e[k, 14], ora["events"][t][k, 14])
+            w = np.where(same & (np.abs(r - ora["reward"][t]) > 0.05))[0][:4]
+            for k in w:
+                print("   reward env", sel[k], "code", spawned[sel[k]], r[k], ora["reward"][t][k], "cont diff cols", np.where(np.abs(e[k] - ora["events"][t][k]) > 1e-3)[0], e[k][np.abs(e[k] - ora["events"][t][k]) > 1e-3], ora["events"][t][k][np.abs(e[k] - ora["events"][t][k]) > 1e-3])
+            bad = np.argsort(-rel)[:5]
+            print("   worst envs", sel[bad], "rel", rel[bad], "obj", idx[sel[bad]], "nrow", gb.probe_field("nrow")[sel[bad]], "same", same[bad])
+        calm = same & (spawned[sel] == 1)
         print(f"t={t} calm {calm.mean():.4f} | calm envs: qpos rel max {rel[calm].max():.2e} obj {dq[calm][:, B:B+3].max():.2e} qvel {dv[calm].max():.2e} obs {np.abs(o - ora['obs'][t])[calm].max():.2e} rew {np.abs(r - ora['reward'][t])[calm].max():.2e} evval {np.abs(e[:, CONT] - ora['events'][t][:, CONT])[calm].max():.2e} | median rel {np.median(rel):.2e} p90 {np.quantile(rel, .9):.2e}")
         print(f"t={t} events identical {same.mean():.4f} done identical {(d.astype(bool) == ora['done'][t]).mean():.4f} | "
               f"qpos gripper rel max {rel.max():.2e} p99 {np.quantile(rel, .99):.2e} | obj pos max {dq[:, B:B+3].max():.2e} p99 {np.quantile(dq[:, B:B+3].max(1), .99):.2e} | "

@@ -129,7 +129,7 @@ def _roll_init(root, n_segments, settings_bytes):
 def _roll_chunk(args):
     """One oracle env per entry: reset(seed, env id, episode) -> spawn -> T x (set_action, action_step, observation,
     is_done, reward, event_state); per step outputs + per step qpos / qvel."""
-    env_ids, episode, obj_idx, xyr, actions, frac, search = args
+    env_ids, episode, obj_idx, xyr, actions, frac, search, stop_at_done = args
     w = _RW
     out = []
     for k, eid in enumerate(env_ids):
@@ -147,21 +147,25 @@ def _roll_chunk(args):
             e.action_step()
             obs.append(e.observation()); done.append(e.is_done()); rew.append(np.float32(e.reward())); ev.append(e.event_state())
             qp.append(e.qpos()); qv.append(e.qvel())
+            if stop_at_done and done[-1]:       # episode over: the remaining steps repeat the terminal outputs (callers mask them)
+                for lst in (obs, rew, done, ev, qp, qv):
+                    lst.extend([lst[-1]] * (actions.shape[0] - 1 - t))
+                break
         out.append((np.stack(obs), np.array(rew, dtype=np.float32), np.array(done), np.stack(ev), np.stack(qp), np.stack(qv)))
     return out
 
 
-def oracle_rollout(N, st, env_ids, episode, obj_idx, xyr, actions, frac=None, cores=None, search=None):
+def oracle_rollout(N, st, env_ids, episode, obj_idx, xyr, actions, frac=None, cores=None, search=None, stop_at_done=False):
     """Oracle trajectories of many independent envs, spread over the host cores (one process per core).
     actions: int [T, n]. Returns dict of arrays with a leading [T, n] (obs, reward, done, events, qpos, qvel)."""
     import multiprocessing as mp
     cores = cores or len(os.sched_getaffinity(0))
     env_ids = np.asarray(env_ids); n = len(env_ids)
-    chunks = np.array_split(np.arange(n), min(n, cores * 4))
+    chunks = np.array_split(np.arange(n), min(n, cores * 8))
     ctx = mp.get_context("spawn")
     with ctx.Pool(cores, initializer=_roll_init, initargs=(ROOT, N, bytes(st.pack()))) as pool:
         res = pool.map(_roll_chunk, [(env_ids[c], episode, np.asarray(obj_idx)[c], np.asarray(xyr)[c], np.asarray(actions)[:, c],
-                                      None if frac is None else np.asarray(frac)[:, c], search) for c in chunks], chunksize=1)
+                                      None if frac is None else np.asarray(frac)[:, c], search, stop_at_done) for c in chunks], chunksize=1)
     flat = [r for ch in res for r in ch]
     keys = ("obs", "reward", "done", "events", "qpos", "qvel")
     return {k: np.stack([f[i] for f in flat], axis=1) for i, k in enumerate(keys)}

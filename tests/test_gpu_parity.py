@@ -14,8 +14,24 @@ pytestmark = pytest.mark.gpu
 DISCRETE = list(range(15)) + [15 + 2 * k for k in range(21)]      # event rows (EventTrack::vectorise)
 CONTINUOUS = [16 + 2 * k for k in range(21)]                       # linear events' last_value
 
-# tolerance per precision: (qpos, qvel, obs, reward, event last_value)
-TOL = {"fp64": (1e-8, 1e-6, 1e-7, 1e-6, 1e-6), "fp32": (5e-3, 3e-1, 2e-2, 1e-2, 5e-1)}
+# tolerance per precision and regime: (qpos, qvel, obs, reward, event last_value). The FP32 bars are <= 3x the maxima
+# measured on B200 (tests/golden/fp32_measured.json, written by this module's session hook; see the table in DESIGN.md):
+#   fp32          free space, plane contact and light finger contact (qpos 1e-4, sensors / reward 1e-3)
+#   fp32_squeeze  objects squeezed between the fingers / flipped by them: a chaotic contact, FP32 drifts from the FP64
+#                 oracle within a few action steps; only these named cases use it
+#                                                 measured maxima over every _compare test of its regime (B200, round 2):
+TOL = {"fp64": (1e-8, 1e-6, 1e-7, 1e-6, 1e-6),           # 7.4e-10, 1.1e-9, 1.2e-10, 3.7e-9, 1.5e-8
+       "fp32": (1.5e-6, 2e-5, 2e-6, 1e-6, 4e-4),         # 4.4e-7,  5.9e-6, 6.3e-7,  0,      1.3e-4
+       "fp32_squeeze": (2.5e-4, 5e-3, 5e-5, 1e-5, 8e-3)}  # 7.5e-5,  1.7e-3, 1.7e-5,  0,      2.8e-3
+MEASURED = {}        # test id -> maxima of (qpos, qvel, obs, reward, event value) errors seen by _compare
+
+
+def _record(vals):
+    import os
+    key = os.environ.get("PYTEST_CURRENT_TEST", "?").split(" ")[0].split("::")[-1]
+    m = MEASURED.setdefault(key, [0.0] * 5)
+    for k, v in enumerate(vals):
+        m[k] = max(m[k], float(v))
 
 OBJECTS = ["cube_fillet_0_3", "cylinder_12_upright_fillet_0_5", "sphere_", "cuboid_221_fillet_10_0",
            "ellipse_1p51_52"]
@@ -30,17 +46,20 @@ def _batch(n, mdl, st, precision):
     return gb
 
 
-def _compare(gb, ob, actions, precision, strict_events=True):
-    tq, tv, to, tr, te = TOL[precision]
+def _compare(gb, ob, actions, precision, strict_events=True, bar=None):
+    tq, tv, to, tr, te = TOL[bar or precision]
     o_g, r_g, d_g, e_g = (v.cpu().numpy() for v in gb.step(actions))
     o_o, r_o, d_o, e_o = ob.step(actions)
     qg, vg = gb.state()
     assert np.isfinite(qg).all()
-    assert np.abs(qg - ob.qpos()).max() < tq
-    assert np.abs(vg - ob.qvel()).max() < tv
-    assert np.abs(o_g - o_o).max() < to
-    assert np.abs(r_g - r_o).max() < tr
-    assert np.abs(e_g[:, CONTINUOUS] - e_o[:, CONTINUOUS]).max() < te
+    errs = (np.abs(qg - ob.qpos()).max(), np.abs(vg - ob.qvel()).max(), np.abs(o_g - o_o).max(),
+            np.abs(r_g - r_o).max(), np.abs(e_g[:, CONTINUOUS] - e_o[:, CONTINUOUS]).max())
+    _record(errs)
+    assert errs[0] < tq, errs
+    assert errs[1] < tv, errs
+    assert errs[2] < to, errs
+    assert errs[3] < tr, errs
+    assert errs[4] < te, errs
     if strict_events:
         assert np.array_equal(e_g[:, DISCRETE], e_o[:, DISCRETE])
         assert np.array_equal(d_g.astype(bool), d_o)
@@ -466,10 +485,13 @@ def test_continuous_actions(precision):
             f[: n // 2] = np.linspace(-0.5, 1.2, n // 2)
         o_g, r_g, d_g, e_g = (v.cpu().numpy() for v in gb.step(a, f))
         o_o, r_o, d_o, e_o = ob.step(a, f)
-        qg, _ = gb.state()
-        assert np.abs(qg - ob.qpos()).max() < tq and np.abs(o_g - o_o).max() < to and np.abs(r_g - r_o).max() < tr
+        qg, vg = gb.state()
+        errs = (np.abs(qg - ob.qpos()).max(), np.abs(vg - ob.qvel()).max(), np.abs(o_g - o_o).max(), np.abs(r_g - r_o).max(),
+                np.abs(e_g[:, CONTINUOUS] - e_o[:, CONTINUOUS]).max())
+        _record(errs)
+        assert errs[0] < tq and errs[2] < to and errs[3] < tr, errs
         assert np.array_equal(e_g[:, DISCRETE], e_o[:, DISCRETE]) and np.array_equal(d_g.astype(bool), d_o)
-        assert np.abs(e_g[:, CONTINUOUS] - e_o[:, CONTINUOUS]).max() < te
+        assert errs[4] < te, errs
     gb.close()
 
 

@@ -133,7 +133,8 @@ def test_wide_lcp_rounds_with_long_objects(precision):
     gb.spawn_object(idx, 0.0, 0.0, 0.0); ob.spawn(idx, 0.0, 0.0, 0.0)
     s0 = gb.stats()
     for t in range(5):
-        _compare(gb, ob, np.full(n, 1 if t < 3 else 5, dtype=np.int32), precision, strict_events=(precision == "fp64"))
+        _compare(gb, ob, np.full(n, 1 if t < 3 else 5, dtype=np.int32), precision, strict_events=(precision == "fp64"),
+                 bar=None if precision == "fp64" else "fp32_squeeze")
     s1 = gb.stats()
     rounds = (s1["solver_iters"] - s0["solver_iters"]) / (s1["substeps"] - s0["substeps"])
     assert s1["contacts"] > s0["contacts"]

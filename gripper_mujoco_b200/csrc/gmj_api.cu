@@ -271,7 +271,11 @@ __global__ void k_dump(const EnvState<T, QC>* envs, int n_envs, int B, double* q
     p[GP_tnext_x] = e.tnext.x; p[GP_tnext_y] = e.tnext.y; p[GP_tnext_z] = e.tnext.z; p[GP_tnext_th] = e.tnext.th;
     p[GP_cumulative_reward] = e.cumulative_reward; p[GP_has_object] = e.has_object; p[GP_obj_index] = e.obj_index;
     p[GP_episode] = e.episode; p[GP_last_reward] = e.last_reward; p[GP_last_done] = e.last_done;
-    p[GP_nrow] = e.nrow_prev;
+    p[GP_nrow] = e.nrow_prev; p[GP_last_nrow] = e.nrow_prev;
+    p[GP_base_x] = e.base_x; p[GP_base_y] = e.base_y; p[GP_base_yaw] = e.base_yaw;
+    for (int k = 0; k < 3; k++) p[GP_read_motor_x + k] = win_read(e, ST_motor + k, 0);
+    p[GP_read_base_x] = win_read(e, ST_basexy, 0); p[GP_read_base_y] = win_read(e, ST_basexy + 1, 0);
+    p[GP_read_base_z] = win_read(e, ST_basez, 0);
     p[GP_niter] = e.st_substeps ? (double)e.st_iters / (double)e.st_substeps : 0.0;   // mean LCP pivoting rounds per substep so far
     p[GP_ncon] = e.st_substeps ? (double)e.st_contacts / (double)e.st_substeps : 0.0;
   }
@@ -733,7 +737,7 @@ int gmj_probe_host(GmjHandle* h, double* probe_host) {
 }
 
 // ------------------------------------------------------------------ allocation-free probe
-// Scratch of gmj_probe_host_noalloc: lives in the library image (every GPU that loads the library holds these 4 MiB
+// Scratch of gmj_probe_host_noalloc: lives in the library image (every GPU that loads the library holds these 5 MiB
 // until exit), shared by every call and every handle on a device -- calls that overlap on the GPU race on it.
 static __device__ __align__(256) double g_noalloc_scratch[(size_t)GMJ_NOALLOC_MAX_ENVS * GMJ_PROBE_LEN];
 // In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is looked up

@@ -18,13 +18,15 @@ SOURCES = ["gmj_api.cu", "gmj_inst.cu", "gmj_step.cuh", "gmj_wide.cuh", "gmj_phy
            "gmj_device.cuh"]
 HEADERS = [os.path.join(_HERE, "..", "include", h) for h in ("gmj.h", "gmj_types.h")]
 
-GMJ_PROBE_LEN = 32
+GMJ_PROBE_LEN = 40
 GMJ_NOALLOC_MAX_ENVS = 16384      # include/gmj.h: static scratch of gmj_probe_host_noalloc
 GMJ_EVENT_STATE_LEN = 57
 PROBE_FIELDS = ["time", "wrist_z", "gauge0", "gauge1", "gauge2", "si_gauge0", "si_gauge1", "si_gauge2",
                 "si_palm", "si_wrist", "ncon", "nrow", "niter", "unstable", "weld_on", "base_z",
                 "tend_x", "tend_y", "tend_z", "tend_th", "tnext_x", "tnext_y", "tnext_z", "tnext_th",
-                "cumulative_reward", "has_object", "obj_index", "episode", "last_reward", "last_done"]
+                "cumulative_reward", "has_object", "obj_index", "episode", "last_reward", "last_done",
+                "last_nrow", "base_x", "base_y", "base_yaw", "read_motor_x", "read_motor_y", "read_motor_z",
+                "read_base_x", "read_base_y", "read_base_z"]
 GP = {n: i for i, n in enumerate(PROBE_FIELDS)}
 
 # every symbol include/gmj.h declares (tests check the .so exports exactly these)

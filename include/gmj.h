@@ -91,11 +91,15 @@ enum { GP_time = 0, GP_wrist_z, GP_gauge0, GP_gauge1, GP_gauge2, GP_si_gauge0, G
        GP_si_palm, GP_si_wrist, GP_ncon, GP_nrow, GP_niter, GP_unstable, GP_weld_on, GP_base_z,
        GP_tend_x, GP_tend_y, GP_tend_z, GP_tend_th, GP_tnext_x, GP_tnext_y, GP_tnext_z, GP_tnext_th,
        GP_cumulative_reward, GP_has_object, GP_obj_index, GP_episode, GP_last_reward, GP_last_done,
-       GMJ_PROBE_LEN = 32 };
+       GP_last_nrow, GP_base_x, GP_base_y, GP_base_yaw,
+       /* latest readings of the state sensors, normalised to [-1, 1] (sim_sensors_.read_*_position(),
+        * src/mjclass.cpp:3160-3178 un-normalises them in get_state_metres) */
+       GP_read_motor_x, GP_read_motor_y, GP_read_motor_z, GP_read_base_x, GP_read_base_y, GP_read_base_z,
+       GMJ_PROBE_LEN = 40 };
 int gmj_probe_host(GmjHandle* h, double* probe_host);
 /* Allocation-free variant of gmj_probe_host. No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (tight serving loops, harnesses that forbid allocation; NOT
- * usable while a stream is being captured: it synchronises and copies to pageable host memory). The device scratch is a static 4 MiB array inside the library (held by every GPU that loads it, until exit),
+ * usable while a stream is being captured: it synchronises and copies to pageable host memory). The device scratch is a static 5 MiB array inside the library (held by every GPU that loads it, until exit),
  * so n_envs <= GMJ_NOALLOC_MAX_ENVS; larger handles are rejected with an error. It calls no cudaMalloc / cudaFree. All
  * calls on a device share the array: calls that overlap on the GPU race; results equal gmj_probe_host's. */
 #define GMJ_NOALLOC_MAX_ENVS 16384

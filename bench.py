@@ -94,9 +94,31 @@ class ClockSampler(threading.Thread):
 
 
 # ----------------------------------------------------------------------------- shared calibration (same config in both arms)
+PRESET = [None]          # --preset: a TrainingManager reward / sensor preset on top of the header defaults
+
+
 def base_settings():
     from gripper_mujoco_b200.settings import Settings
     st = Settings()
+    if PRESET[0]:
+        # rl/TrainingManager.py configure_env: wipe -> apply_env_settings -> create_reward_function, with DISCRETE actions
+        # (one action per step, the fused gmj_step; the continuous variant sets every action per step through
+        # gmj_set_action and is covered by tests/test_presets.py)
+        from gripper_mujoco_b200 import training_presets as tp
+
+        class _Env:
+            class params:
+                max_episode_steps = EPISODE_CAP
+
+            class mj:
+                pass
+        _Env.mj.set = st
+        _Env.mj.set_sensor_noise_and_normalisation_to = staticmethod(lambda v: (st.set_use_normalisation(v), st.set_use_noise(v)))
+        _Env.mj.yield_load = staticmethod(lambda: 3.458)
+        cfg = tp.preset(PRESET[0])
+        cfg["cpp"]["continous_actions"] = False
+        cfg["cpp"]["use_termination_action"] = True
+        tp.configure_env(_Env, cfg)
     st.debug = False
     st.random_seed = 1234
     st.set_use_noise(True)
@@ -104,7 +126,8 @@ def base_settings():
 
 
 def calib_path(N: int) -> str:
-    return os.path.join(tempfile.gettempdir(), f"gmj_bench_calibration_N{N}.pkl")
+    tag = f"_{PRESET[0]}" if PRESET[0] else ""
+    return os.path.join(tempfile.gettempdir(), f"gmj_bench_calibration_N{N}{tag}.pkl")
 
 
 def shared_calibration(N: int, how: str, device: int = 0):
@@ -143,6 +166,8 @@ def workload_config(args, N, envs, st, workload):
            (24, 1024): "configs[4] sweep point"}.get((N, envs), "custom")
     acts = "random discrete actions" if workload == "random" else \
         "contact-heavy: scripted prefix per episode (close x30, tilt x10, palm x20, base-Z up x15) then random discrete actions"
+    if PRESET[0]:
+        acts += f", TrainingManager preset '{PRESET[0]}' (sensors, noise, reward function; discrete actions + termination action)"
     return {"workload": f"{cfg}: {envs} envs/GPU, {N}-segment fingers, set9_fullset-like 1750 objects, {acts}, "
                         f"auto-reset (cap {EPISODE_CAP}), spawn_into_scene +-10 mm / +-90 deg with MjEnv's retry policy",
             "envs_per_gpu": envs, "segments": N, "timestep": st.mujoco_timestep,
@@ -402,7 +427,10 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the extra.configs sub-results")
+    ap.add_argument("--preset", default=None, choices=["sensor_mixed_v1", "sparse", "termination_action_v1", "MAT_liftonly"],
+                    help="run under a TrainingManager preset (rl/TrainingManager.py:804-1268) instead of the header defaults")
     args = ap.parse_args()
+    PRESET[0] = args.preset
     if args.impl == "reference":
         return reference_arm(args)
     args.warmup = max(args.warmup, 3)
@@ -425,7 +453,7 @@ def main():
     K, W = args.steps, args.warmup
     head = run_config(args, args.segments, args.envs, K, W, args.workload, rank, world, local, headline=True)
     extras = []
-    default_run = (args.segments, args.envs, args.workload) == (5, 4096, "random")
+    default_run = (args.segments, args.envs, args.workload, args.preset) == (5, 4096, "random", None)
     if not args.no_extras and default_run:
         # BASELINE.json configs[2] / [3]: 16384 envs per GPU, 8-segment fingers, contact-heavy grasp-and-lift episodes
         # (at --gpus 8 this IS configs[3]: 131072 envs, transitions gathered to rank 0 inside e2e); configs[4]: one point

@@ -221,6 +221,31 @@ class Settings:
         for n in ACTION_NAMES:
             getattr(self, n).continous = bool(v)
 
+    def set_all_action_use(self, v):                    # src/mjclass.cpp:5366-5386
+        for n in ACTION_NAMES:
+            getattr(self, n).in_use = bool(v)
+
+    def set_all_action_value(self, v):                  # src/mjclass.cpp:5388-5397
+        for n in ACTION_NAMES:
+            getattr(self, n).value = float(v)
+
+    def set_all_action_sign(self, v):                   # src/mjclass.cpp:5399-5416
+        if v not in (-1, 1):
+            raise RuntimeError("MjType::Settings::set_all_action_sign recieved a value not either +1 or -1")
+        for n in ACTION_NAMES:
+            getattr(self, n).sign = int(v)
+
+    def get_settings(self) -> str:
+        """MjType::Settings::get_settings (src/mjclass.cpp:4967-5060): every field as text, one per line."""
+        rows = [f"{k} = {getattr(self, k)}" for k in list(GENERAL_DEFAULTS) + list(EXTRA_DEFAULTS)]
+        for n in SENSOR_NAMES:
+            rows.append(f"{n} = {getattr(self, n).row()}")
+        for n in ACTION_NAMES:
+            rows.append(f"{n} = {getattr(self, n).row()}")
+        for n in BINARY_NAMES + LINEAR_NAMES:
+            rows.append(f"{n} = {getattr(self, n).row()}")
+        return "\n".join(rows)
+
     def scale_rewards(self, scale):
         for n in BINARY_NAMES + LINEAR_NAMES:
             getattr(self, n).reward *= scale

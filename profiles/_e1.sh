@@ -1,2 +1,2 @@
 mkdir -p gpurun_out
-(timeout 900 python -m pytest tests/test_gpu_mjenv_sequence.py tests/test_zz_no_alloc.py -m gpu -q -x > gpurun_out/r2_seq.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r2_seq.log); tail -40 gpurun_out/r2_seq.log | cut -c1-300
+timeout 600 python bench.py --preset termination_action_v1 --steps 10 --warmup 3 --cpu-seconds 6 --no-extras > gpurun_out/r2_bench_preset.json 2> gpurun_out/r2_bench_preset.err; echo "rc=$?"; tail -c 300 gpurun_out/r2_bench_preset.err; cut -c1-1200 gpurun_out/r2_bench_preset.json

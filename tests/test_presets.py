@@ -1,0 +1,169 @@
+"""TrainingManager's environment presets (gripper_mujoco_b200/training_presets.py) against the values the reference's
+code produces (rl/TrainingManager.py:804-1268), and -- on the GPU -- the CUDA path against the oracle under a preset."""
+import numpy as np
+import pytest
+
+from gripper_mujoco_b200 import training_presets as tp
+from gripper_mujoco_b200.model import GripperParams
+from gripper_mujoco_b200.settings import Settings
+
+
+class _Mj:
+    def __init__(self):
+        self.set = Settings()
+        self.params = GripperParams(num_segments=8)
+
+    def set_sensor_noise_and_normalisation_to(self, v):
+        self.set.set_use_normalisation(v); self.set.set_use_noise(v)
+
+    def yield_load(self):
+        from gripper_mujoco_b200 import calibration
+        return calibration.yield_load(self.params)
+
+
+class _Env:
+    class P:
+        max_episode_steps = 250
+
+    def __init__(self):
+        self.mj, self.params = _Mj(), _Env.P()
+
+
+def test_every_field_the_presets_touch_exists_on_settings():
+    fresh = Settings()
+    d = tp.default_settings()
+    for k in d["cpp"]:
+        if k not in ("action", "sensor"):
+            assert hasattr(fresh, k), k
+    for k in ("auto_set_timestep", "auto_calibrate_gauges", "auto_sim_steps", "auto_exceed_lateral_lim", "curve_validation",
+              "render_on_step", "use_termination_action", "quit_if_cap_exceeded", "reward_cap_lower_bound",
+              "reward_cap_upper_bound", "use_HER", "sensor_noise_mag", "state_noise_mag", "base_position_noise"):
+        assert hasattr(fresh, k), k
+    for nm in tp.ACTIONS + tp.SENSORS:
+        assert hasattr(fresh, nm), nm
+
+
+def test_default_preset_sensor_mixed_v1():
+    env = tp.configure_env(_Env())
+    st = env.mj.set
+    assert st.continous_actions and st.n_actions() == 4                       # prismatic X, revolute Y, gripper Z, base Z
+    assert (st.gripper_prismatic_X.value, st.gripper_prismatic_X.sign) == (2e-3, -1) and not st.base_X.in_use
+    assert st.sensor_n_prev_steps == 3 and st.state_sample_mode == 4 and st.sensor_sample_mode == 2
+    assert st.bending_gauge.in_use and st.palm_sensor.in_use and st.wrist_sensor_Z.in_use and not st.base_state_sensor_XY.in_use
+    assert st.base_state_sensor_Z.noise_overriden and (st.base_state_sensor_Z.noise_mu, st.base_state_sensor_Z.noise_std) == (0.1, 0.0)
+    assert st.bending_gauge.use_noise and st.bending_gauge.use_normalisation
+    k = 100 / 250
+    assert np.isclose(st.step_num.reward, -0.01 * k) and st.step_num.trigger == 1
+    assert np.isclose(st.lifted.reward, 0.002 * k) and np.isclose(st.object_stable.reward, 0.002 * k)
+    assert np.allclose([st.good_bend_sensor.reward, st.good_bend_sensor.min, st.good_bend_sensor.max], [0.002 * k, 0.0, 1.0])
+    assert np.allclose([st.exceed_bend_sensor.reward, st.exceed_bend_sensor.min, st.exceed_bend_sensor.max], [-0.002 * k, 4.0, 5.0])
+    assert np.allclose([st.exceed_wrist_sensor.min, st.exceed_wrist_sensor.max], [6.0, 8.0])
+    assert np.allclose([st.action_penalty_sq.reward, st.action_penalty_sq.min, st.action_penalty_sq.max], [-0.004 * k, 0.1, 3.0])
+    assert st.action_penalty_lin.trigger == 10000 and st.action_penalty_lin.reward == 0          # not used: stays wiped
+    # set after scale_rewards, so not scaled
+    assert (st.stable_height.reward, st.stable_height.done) == (1.0, 1) and (st.oob.reward, st.oob.done) == (-1.0, 1)
+    assert (st.dangerous_bend_sensor.reward, st.dangerous_bend_sensor.done, st.dangerous_bend_sensor.min) == (-1.0, 1, 5.0)
+    assert st.dangerous_wrist_sensor.min == 8.0 and st.dangerous_palm_sensor.trigger == 1
+    assert st.stable_termination.trigger == 10000 and st.successful_grasp.reward == 0             # wiped, never set
+    st.pack()
+
+
+def test_other_styles_and_errors():
+    env = tp.configure_env(_Env(), tp.preset("termination_action_v1"))
+    st = env.mj.set
+    assert st.use_termination_action and st.n_actions() == 5
+    assert (st.stable_termination.reward, st.stable_termination.done) == (1.0, 1)
+    assert (st.failed_termination.reward, st.failed_termination.done) == (-1.0, 1)
+    assert st.stable_height.trigger == 10000
+    env = tp.configure_env(_Env(), tp.preset("sparse"))
+    assert env.mj.set.step_num.reward == 0 and env.mj.set.stable_height.done == 1 and env.mj.set.good_bend_sensor.trigger == 10000
+    env = tp.configure_env(_Env(), tp.preset("MAT_liftonly"))
+    st = env.mj.set
+    assert (st.lifted_termination.reward, st.lifted_termination.done) == (1.0, 1) and st.failed_termination.reward == 0.0
+    assert st.dangerous_bend_sensor.reward == 0.0 and st.dangerous_bend_sensor.done == 1 and st.oob.done == 1
+    env = tp.configure_env(_Env(), tp.preset("sensor_mixed_v1", options=["terminate_on_exceed_limits"], stable_trigger=3))
+    assert (env.mj.set.exceed_limits.reward, env.mj.set.exceed_limits.done, env.mj.set.exceed_limits.trigger) == (-1.0, 1, 3)
+    assert env.mj.set.object_stable.trigger == 3
+    with pytest.raises(RuntimeError):
+        tp.preset("no_such_style")
+    bad = tp.preset("sensor_mixed_v1")
+    bad["reward"]["bend"]["dangerous"] = 3.0              # below exceed (stable_lim = 4)
+    with pytest.raises(RuntimeError, match="xBend > dBend"):
+        tp.configure_env(_Env(), bad)
+    yl = tp.preset("sensor_mixed_v1")
+    yl["reward"]["bend"]["dangerous"] = "yield"
+    yl["reward"]["bend"]["exceed"] = 3.0                  # the 0.9 x 28 mm finger yields at 3.46 N, below stable_lim
+    env = tp.configure_env(_Env(), yl)
+    assert abs(env.mj.set.dangerous_bend_sensor.min - env.mj.yield_load()) < 1e-9
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("style", ["sensor_mixed_v1", "termination_action_v1"])
+def test_preset_parity_gpu_vs_oracle(style):
+    """The preset's settings on both sides (N = 8 fingers, 0.86 mm thick; continuous actions: every in-use action is set
+    each step as MjEnv._set_action does, rl/env/MjEnv.py:585-599): rewards, done flags and event rows equal, observation
+    (3-step sensor history, sample mode 2 / 4, noise on) within the FP32 bar."""
+    from common import OracleBatch, objects, oracle_calibration
+    from gripper_mujoco_b200.batch import GripperBatch
+    from gripper_mujoco_b200.model import build_model
+    env = _Env()
+    env.mj.params.finger_thickness = 0.86e-3
+    tp.configure_env(env, tp.preset(style))
+    st, prm = env.mj.set, env.mj.params
+    st.mujoco_timestep, st.sim_steps_per_action = 3.0e-3, 67          # what the auto-calibration finds for this finger, fixed here
+    st.auto_set_timestep = st.auto_calibrate_gauges = st.auto_sim_steps = False
+    st.bending_gauge.normalise = 2.3
+    st.random_seed, st.use_noise_seeded = 99, 1
+    rq = oracle_calibration(8)
+    st.reset_qpos_base = float(rq[0])
+    for k in range(7):
+        setattr(st, f"reset_qpos_g{k}", float(rq[1 + k]))
+    mdl = build_model(prm)
+    n = 16
+    gb = GripperBatch(n, mdl, st, precision="fp32"); gb.set_objects(objects())
+    ob = OracleBatch(n, mdl, st)
+    gb.reset(); ob.reset()
+    rng = np.random.default_rng(8)
+    idx = rng.integers(0, len(objects()), n).astype(np.int32)
+    x = (rng.integers(-4, 5, n) * 2e-3).astype(np.float32)
+    gb.spawn_object(idx, x, -x, 0.2); ob.spawn(idx, x, -x, 0.2)
+    n_act = gb.n_actions
+    assert n_act == st.n_actions()
+    DISC = list(range(15)) + [15 + 2 * k for k in range(21)]
+    worst = np.zeros(2); squeeze = np.zeros(2); agree = np.ones(n, bool); touched = np.zeros(n, bool); ended = np.zeros(n, bool)
+    for t in range(12):
+        f = rng.uniform(-1, 1, (n_act, n)).astype(np.float32)
+        f[0] = np.abs(f[0]) * (1 if t < 9 else -1)                       # mostly closing
+        if st.use_termination_action:
+            f[n_act - 1] = np.where((np.arange(n) % 4 == 0) & (t == 10), 0.95, -0.5)   # a quarter of the envs terminate at t = 10
+        for a in range(n_act):                                           # MjEnv._set_action, continuous branch
+            act = np.full(n, a, dtype=np.int32)
+            gb.set_action(act, f[a])
+            for i, e in enumerate(ob.envs):
+                assert e.set_action(a, float(f[a, i])) == 0
+        gb.action_step()
+        o_g, r_g, d_g, e_g = (v.cpu().numpy() for v in gb.observe())
+        for e in ob.envs:
+            e.action_step()
+        o_o = np.stack([e.observation() for e in ob.envs]); d_o = np.array([e.is_done() for e in ob.envs])
+        r_o = np.array([e.reward() for e in ob.envs], dtype=np.float32); e_o = np.stack([e.event_state() for e in ob.envs])
+        agree &= (e_g[:, DISC] == e_o[:, DISC]).all(1)                  # an env whose contact switched a step apart has left
+        assert np.array_equal(d_g.astype(bool)[agree], d_o[agree]), t
+        ended |= d_o
+        if t < 8:
+            assert agree.all(), t
+        touched |= e_o[:, 7] > 0                                         # object_contact row: a finger touches the object
+        free, grip = agree & ~touched, agree & touched
+        for w, m in ((worst, free), (squeeze, grip)):
+            if m.any():
+                w[:] = np.maximum(w, [np.abs(o_g - o_o)[m].max(), np.abs(r_g - r_o)[m].max()])
+    print(f"\nMEASURED preset {style}: obs {worst[0]:.2e} reward {worst[1]:.2e} | envs in finger contact: obs {squeeze[0]:.2e} reward {squeeze[1]:.2e} | envs with identical event rows {agree.mean():.3f}")
+    assert agree.mean() >= 0.85, agree.mean()
+    # envs without an object_contact event so far: measured 4.8e-4 / 1.9e-9 (one env whose tall cylinder grazes a finger below
+    # the event's force threshold; all others < 1e-5)
+    assert worst[0] < 1.5e-3 and worst[1] < 3e-7, worst
+    assert touched.mean() > 0.3
+    assert squeeze[0] < 2.5e-2 and squeeze[1] < 2e-5, squeeze         # measured 8.6e-3 / 4.4e-6 (objects in the fingers' grip)
+    if st.use_termination_action:
+        assert ended.sum() >= n // 4, "the termination action ended a quarter of the episodes"
+    gb.close()

@@ -4,13 +4,18 @@
  * only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs do.
  *
  * PARITY STATUS
- *  - Non-physics path (motor kinematics, stepper, welds toggling, sensors, sliding windows,
- *    samplers, events, reward, done, observation): restated line by line from the reference
- *    sources cited at each function, and PINNED against the reference's own src/gripper.cpp and
- *    src/slidingwindow.h compiled verbatim into oracle/_ref (see oracle/Makefile, tests/golden).
- *  - Physics (mj_step1 / mj_step2): the arithmetic lives in MuJoCo 2.1.5 (libmujoco, not
- *    vendored, not installable here). It is restated from MuJoCo's published algorithm for this
- *    scene class. PARITY UNPINNED for physics: no MuJoCo trajectories exist in this container.
+ *  - Motor kinematics, limits, stepper, sliding windows: PINNED against the reference's own src/gripper.cpp and
+ *    src/slidingwindow.h compiled verbatim into oracle/_ref/libgripper_ref.so (tests/test_oracle_golden.py).
+ *  - The whole non-physics tail (set_action, the action_step loop's sensor sampling with noise, update_env, events,
+ *    reward, is_done, get_observation in every sample mode, spawn_into_scene's search and Box2d SAT): PINNED against
+ *    the reference's own src/mjclass.cpp compiled in place over stub MuJoCo headers and driven by scripted physics
+ *    observables (oracle/ref_tail_shim.cpp, oracle/_ref/libmjclass_ref.so); or_set_script() runs this restatement on
+ *    the same script and tests/test_ref_tail.py compares with tests/golden/tail_golden.npz bit for bit.
+ *  - Physics (mj_step1 / mj_step2): the arithmetic lives in MuJoCo 2.1.5 (libmujoco, not vendored, not installable
+ *    here). It is restated from MuJoCo's published algorithm for this scene class. PARITY UNPINNED for physics: no
+ *    MuJoCo trajectories exist in this container (route to a pin: tools/mujoco_pin.py).
+ *  - or_set_fast(): timed-baseline mode for bench.py's CPU arms (direct active-set solve, skyline Cholesky); equals
+ *    the checker mode to 1e-16 (tests/test_host_logic.py).
  *
  * double = mjtNum, float = luke::gfloat (src/customtypes.h:22).
  */

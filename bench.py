@@ -409,6 +409,8 @@ def run_config(args, N, envs, K, W, workload, rank, world, local, headline):
             "roofline": roofline, "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "clocks": clocks, "gpu_launches": gpu_launches, "steps": K, "warmup": W,
             "stats": {"unstable_resets": s2["unstable_resets"] - s0["unstable_resets"], "contact_overflow": s2["contact_overflow"],
+                      "relaxed_solves_per_substep": (s2["relaxed_solves"] - s1["relaxed_solves"]) / sub,
+                      "capped_solves": s2["capped_solves"] - s1["capped_solves"],
                       "calibration_s": t_cal, "calibration_source": cal_src, "preroll_steps": PREROLL,
                       "torch_bookkeeping_launches_per_step": 4},
             "settings": st}

@@ -49,9 +49,9 @@ __global__ void k_reset(EnvState<T, QC>* envs, const DevModelS<T>* Mp, const Dev
   const DevModelS<T>& M = *Mp; const DevSettings& S = *Sp;
   const int N = M.N, NL = N + 2, B = M.B;
   uint32_t episode = e.episode + 1;
-  unsigned long long c0 = e.st_contacts, c1 = e.st_rows, c2 = e.st_iters, c3 = e.st_substeps; unsigned int c4 = e.st_unstable + (e.unstable ? 1 : 0), c5 = e.st_overflow;
+  unsigned long long c0 = e.st_contacts, c1 = e.st_rows, c2 = e.st_iters, c3 = e.st_substeps; unsigned int c4 = e.st_unstable + (e.unstable ? 1 : 0), c5 = e.st_overflow, c6 = e.st_relaxed, c7 = e.st_capped;
   memset(&e, 0, sizeof(EnvState<T, QC>));
-  e.st_contacts = c0; e.st_rows = c1; e.st_iters = c2; e.st_substeps = c3; e.st_unstable = c4; e.st_overflow = c5;
+  e.st_contacts = c0; e.st_rows = c1; e.st_iters = c2; e.st_substeps = c3; e.st_unstable = c4; e.st_overflow = c5; e.st_relaxed = c6; e.st_capped = c7;
   e.episode = episode; e.env_id = env_id_offset + env; e.rng_ctr = episode << 12;
   g_reset(e.tend); g_reset(e.tnext);
   for (int i = 0; i < B; i++) e.qpos[i] = M.qpos0[i];
@@ -309,7 +309,7 @@ __global__ void k_stats(const EnvState<T, QC>* envs, int n_envs, unsigned long l
   const EnvState<T, QC>& e = envs[env];
   atomicAdd(&out[0], e.st_substeps); atomicAdd(&out[1], (unsigned long long)(e.st_unstable + (e.unstable ? 1 : 0)));
   atomicAdd(&out[2], e.st_contacts); atomicAdd(&out[3], e.st_rows); atomicAdd(&out[4], e.st_iters);
-  atomicAdd(&out[5], (unsigned long long)e.st_overflow);
+  atomicAdd(&out[5], (unsigned long long)e.st_overflow); atomicAdd(&out[6], (unsigned long long)e.st_relaxed); atomicAdd(&out[7], (unsigned long long)e.st_capped);
 }
 
 // EventTrack of every env (MjType::EventTrack, src/mjclass.h:575-647): row / abs counters and last values
@@ -819,7 +819,7 @@ int gmj_stats(GmjHandle* h, GmjStats* out) {
   unsigned long long v[8];
   CK(cudaMemcpy(v, h->stats_dev, sizeof(v), cudaMemcpyDeviceToHost));
   out->substeps = (int64_t)v[0]; out->unstable_resets = (int64_t)v[1]; out->contacts = (int64_t)v[2];
-  out->rows = (int64_t)v[3]; out->solver_iters = (int64_t)v[4]; out->contact_overflow = (int64_t)v[5];
+  out->rows = (int64_t)v[3]; out->solver_iters = (int64_t)v[4]; out->contact_overflow = (int64_t)v[5]; out->relaxed_solves = (int64_t)v[6]; out->capped_solves = (int64_t)v[7];
   int ef = 0;
   CK(cudaMemcpy(&ef, h->err_flag, sizeof(int), cudaMemcpyDeviceToHost));
   if (ef) { CK(cudaMemset(h->err_flag, 0, sizeof(int))); g_err = ef == 1 ? "an action index was out of range" : (ef == 2 ? "a spawn object index was out of range" : "spawn ranges give more candidates than the device search holds (1024 positions, 128 rotations)"); return 2; }

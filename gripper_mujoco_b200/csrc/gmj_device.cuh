@@ -52,6 +52,7 @@ struct EnvState {
   uint32_t rng_ctr, env_id, episode, obj_index;
   unsigned long long st_contacts, st_rows, st_iters, st_substeps;
   unsigned int st_unstable, st_overflow, pending_extra, sort_key;   // pending_extra: lift substeps owed by set_action
+  unsigned int st_relaxed, st_capped;   // constraint solves accepted under a widened feasibility tolerance (3+ rounds) / at the round cap while infeasible
   int mpr_prev;                     // MPR passes (0-2: finger plates, hooks) the last substep ran: load key of the lockstep sort
 #ifdef GMJ_PROF
   unsigned int prof[12];            // development build: cycles per phase (gmj_physics.cuh GMJ_PROF_*)

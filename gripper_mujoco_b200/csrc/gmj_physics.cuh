@@ -396,7 +396,7 @@ __device__ int lcp_solve_impl(WarpShared<T, N, QC>& ws, int nr, int lane, const 
     bool bad1 = (TWO && r1 < nr) && type[1] != ROW_EQ && (act1 ? x1 < -tolf : w1 < -tolw);
     const unsigned b0 = __ballot_sync(GMJ_FULL, bad0), b1 = __ballot_sync(GMJ_FULL, bad1);
     const int ninf = __popc(b0) + __popc(b1);
-    if (ninf == 0 || it >= maxit) break;
+    if (ninf == 0 || it >= maxit) { if (it > GMJ_LCP_GROW_FROM) it |= 1 << 16; if (ninf != 0) it |= 1 << 17; break; }
     bool block = true;
     if (ninf < best) { best = ninf; patience = 3; }
     else if (patience > 0) patience--;
@@ -1024,7 +1024,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   if (lane == 0) {
     if (anybad) e.unstable = 1;
     e.time += dtd;
-    e.st_substeps++; e.st_contacts += ncon; e.st_rows += nr; e.st_iters += iters;
+    e.st_substeps++; e.st_contacts += ncon; e.st_rows += nr; e.st_iters += iters & 0xffff; e.st_relaxed += (iters >> 16) & 1; e.st_capped += (iters >> 17) & 1;
   }
   __syncwarp();
 }

@@ -281,7 +281,7 @@ __device__ int primal_solve(WarpShared<T, N>& ws, const Topo<N>& tp, const T* so
     const bool bad1 = two && r1 < nr && type[1] != ROW_EQ && (act[1] ? f1 < -tolf : j1 < -tolw);
     const unsigned b0 = __ballot_sync(GMJ_FULL, bad0), b1 = __ballot_sync(GMJ_FULL, bad1);
     const int ninf = __popc(b0) + __popc(b1);
-    if (ninf == 0 || it >= maxit) break;
+    if (ninf == 0 || it >= maxit) { if (it > GMJ_LCP_GROW_FROM) it |= 1 << 16; if (ninf != 0) it |= 1 << 17; break; }
     bool block = true;
     if (ninf < best) { best = ninf; patience = 3; }
     else if (patience > 0) patience--;

@@ -781,6 +781,6 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
   if (tid == 0) {
     if (ws.ebad) e.unstable = 1;
     e.time += dtd;
-    e.st_substeps++; e.st_contacts += ncon; e.st_rows += nr; e.st_iters += iters;
+    e.st_substeps++; e.st_contacts += ncon; e.st_rows += nr; e.st_iters += iters & 0xffff; e.st_relaxed += (iters >> 16) & 1; e.st_capped += (iters >> 17) & 1;
   }
 }

@@ -38,7 +38,8 @@ SYMBOLS = ["gmj_create", "gmj_destroy", "gmj_set_settings", "gmj_set_objects", "
 
 class GmjStats(C.Structure):
     _fields_ = [("substeps", C.c_int64), ("unstable_resets", C.c_int64), ("contacts", C.c_int64),
-                ("rows", C.c_int64), ("solver_iters", C.c_int64), ("contact_overflow", C.c_int64)]
+                ("rows", C.c_int64), ("solver_iters", C.c_int64), ("contact_overflow", C.c_int64),
+                ("relaxed_solves", C.c_int64), ("capped_solves", C.c_int64)]
 
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]

@@ -173,8 +173,10 @@ typedef struct GmjStats {
   int64_t unstable_resets;   /* BADQACC-equivalent events (src/myfunctions.cpp:4233) */
   int64_t contacts;          /* sum of ncon over substeps                         */
   int64_t rows;              /* sum of constraint rows over substeps              */
-  int64_t solver_iters;      /* sum of PGS sweeps                                 */
+  int64_t solver_iters;      /* sum of active-set pivoting rounds                 */
   int64_t contact_overflow;  /* contacts dropped because > GMJ_MAXCON             */
+  int64_t relaxed_solves;    /* constraint solves that needed 3+ pivoting rounds: accepted under the widened feasibility tolerance */
+  int64_t capped_solves;     /* constraint solves that hit the round cap with an infeasible active set    */
 } GmjStats;
 
 #ifdef __cplusplus

@@ -1,5 +1,7 @@
 """Development driver: per-step largest gap of the continuous event values (fp32 CUDA vs oracle)."""
 import numpy as np
+import os, sys  # development script (moved out of tests/): make tests/common.py importable
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from common import OracleBatch, find_object, make_pair, objects
 from gripper_mujoco_b200.batch import GripperBatch
 from gripper_mujoco_b200.settings import LINEAR_NAMES

@@ -1,4 +1,6 @@
 import numpy as np, sys
+import os, sys  # development script (moved out of tests/): make tests/common.py importable
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from common import OracleBatch, find_object, make_pair, objects
 from gripper_mujoco_b200.batch import GripperBatch
 n = 1

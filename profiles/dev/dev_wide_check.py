@@ -1,10 +1,12 @@
 """Development aid (not collected by pytest): wide-kernel (N = 16 / 24) parity against the oracle, printing
-the per-step differences instead of asserting. Usage: python tests/dev_wide_check.py [fp64|fp32] [N ...]"""
+the per-step differences instead of asserting. Usage: python profiles/dev/dev_wide_check.py [fp64|fp32] [N ...]"""
 import sys
 import time
 
 import numpy as np
 
+import os, sys  # development script (moved out of tests/): make tests/common.py importable
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from common import OracleBatch, find_object, make_pair, objects
 
 DISCRETE = list(range(15)) + [15 + 2 * k for k in range(21)]

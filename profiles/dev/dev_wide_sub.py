@@ -1,6 +1,8 @@
 """Development aid: one wide-kernel substep against the oracle, per-dof differences."""
 import sys
 import numpy as np
+import os, sys  # development script (moved out of tests/): make tests/common.py importable
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from common import OracleBatch, make_pair, objects
 from gripper_mujoco_b200.batch import GripperBatch
 np.set_printoptions(linewidth=220, precision=3, suppress=False)

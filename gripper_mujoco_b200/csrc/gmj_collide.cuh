@@ -175,3 +175,45 @@ __device__ GMJ_CINL int plane_candidates(const Shape<T>& s, T gz, V3<T>* pts, T*
   }
   return n;
 }
+
+// Candidate `i` of plane_candidates() computed alone (one lane per candidate): returns the candidate count n (uniform
+// over lanes); p / d are set when i < n, d = 1 (not penetrating) otherwise. Same arithmetic as plane_candidates().
+template <typename T>
+__device__ GMJ_CINL int plane_candidate_lane(const Shape<T>& s, T gz, int i, V3<T>& p, T& d) {
+  d = T(1); p = mk<T>(0, 0, 0);
+  if (s.pos.z - gz - shape_bound(s) > 0) return 0;
+  int n;
+  if (s.type == GMJ_GEOM_ELLIPSOID) {
+    n = 1;
+    if (i == 0) { p = support(s, mk<T>(0, 0, -1)); d = p.z - gz; }
+  } else if (s.type == GMJ_GEOM_BOX) {
+    n = 8;
+    if (i < 8) {
+      V3<T> c = mk<T>((i & 1 ? 1 : -1) * s.size.x, (i & 2 ? 1 : -1) * s.size.y, (i & 4 ? 1 : -1) * s.size.z);
+      p = mul(s.R, c) + s.pos;
+      p.z -= s.round;
+      d = p.z - gz;
+    }
+  } else {
+    n = 4;
+    V3<T> axis = mk<T>(s.R.m[2], s.R.m[5], s.R.m[8]);
+    T prj = -axis.z;
+    if (prj < 0) { axis = axis * T(-1); prj = -prj; }
+    V3<T> vec = mk<T>(-axis.x * prj, -axis.y * prj, T(-1) - axis.z * prj);
+    T len = sqrtT<T>(dot(vec, vec));
+    if (len < T(1e-12)) { vec = mk<T>(s.R.m[0], s.R.m[3], s.R.m[6]); len = 1; }
+    vec = vec * (s.size.x * rcpT<T>(len));
+    V3<T> ax = axis * s.size.z;
+    if (i < 4) {
+      if (i == 0) p = s.pos + ax + vec;
+      else if (i == 1) p = s.pos - ax + vec;
+      else {
+        V3<T> v1 = normalized(cross(vec, axis)) * (s.size.x * T(0.8660254037844386));
+        p = (i == 2) ? s.pos + ax - vec * T(0.5) - v1 : s.pos + ax - vec * T(0.5) + v1;
+      }
+      p.z -= s.round;
+      d = p.z - gz;
+    }
+  }
+  return n;
+}

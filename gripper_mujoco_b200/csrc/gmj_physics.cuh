@@ -667,21 +667,25 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
     cn.dist = dist; cn.mu = mu; cn.body1 = b1; cn.body2 = b2; cn.cls1 = c1; cn.cls2 = c2;
     cn.force[0] = cn.force[1] = cn.force[2] = 0; cn.row = -1;
   };
-  // (1) object vs ground: uniform work, lane 0 writes
+  // (1) object vs ground: lane i forms candidate i (8 box corners / 4 cylinder points / 1 ellipsoid point); the up to four
+  // deepest penetrating ones become contacts, deepest first, ties by candidate index. (The serial version kept 8 points
+  // per lane in local memory: ncu r2, 2 % of the stall samples.)
   if (has_obj) {
-    V3<T> pts[8]; T dd[8];
-    int n = plane_candidates<T>(so, gz, pts, dd);
-    T mu = maxT<T>(M.ground_friction, ofric);
-    for (int k = 0; k < 4 && k < n; k++) {
-      int best = -1;
-      for (int i = 0; i < n; i++) if (dd[i] < 0 && (best < 0 || dd[i] < dd[best])) best = i;
-      if (best < 0) break;
-      if (ncon < GMJ_MAXCON) {
-        if (lane == 0) { V3<T> pp = pts[best]; pp.z -= T(0.5) * dd[best]; add_contact(pp, mk<T>(0, 0, 1), dd[best], mu, -1, GMJ_CLS_GROUND, B, GMJ_CLS_OBJECT, ncon); }
-        ncon++;
-      }
-      dd[best] = 1;
+    V3<T> pc; T dc;
+    plane_candidate_lane<T>(so, gz, lane, pc, dc);
+    int rank = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) { const T dj = __shfl_sync(GMJ_FULL, dc, j); rank += (dj < 0 && (dj < dc || (dj == dc && j < lane))) ? 1 : 0; }
+    const bool pen = lane < 8 && dc < 0;
+    int np = __popc(__ballot_sync(GMJ_FULL, pen));
+    if (np > 4) np = 4;
+    if (np > GMJ_MAXCON - ncon) np = GMJ_MAXCON - ncon;
+    if (pen && rank < np) {
+      V3<T> pp = pc; pp.z -= T(0.5) * dc;
+      add_contact(pp, mk<T>(0, 0, 1), dc, maxT<T>(M.ground_friction, ofric), -1, GMJ_CLS_GROUND, B, GMJ_CLS_OBJECT, ncon + rank);
     }
+    ncon += np;
+    __syncwarp();
   }
   // per-lane geoms: primary (segment plate / palm cylinder) and hook plate on the tip lanes
   Shape<T> sg, sh;

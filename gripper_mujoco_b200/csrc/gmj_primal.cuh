@@ -17,8 +17,14 @@
 // linear in the row count. The pivoting rule (flip every violated row, Murty's least-index rule after three
 // non-improving rounds), tolerances and warm start are those of the dual solver; the solution is the same unique one.
 #pragma once
+#include <type_traits>
 
 // scratch laid over the packed-A storage of WarpShared (unused in primal mode)
+// compile-time loop: f(std::integral_constant<int, I>) for I in [I0, I1)
+template <int I0, int I1, class F> __device__ __forceinline__ void static_for(F&& f) {
+  if constexpr (I0 < I1) { f(std::integral_constant<int, I0>{}); static_for<I0 + 1, I1>(f); }
+}
+
 template <typename T, int N> struct PrimalScratch {
   static constexpr int NL = N + 2, B = 3 * N + 8;
   T Lc[3][NL][NL + 1];      // finger blocks of the factor, for the column walk of the back substitution
@@ -119,40 +125,38 @@ __device__ __forceinline__ void primal_factor_solve(WarpShared<T, N>& ws, Primal
     if (em == en) sc.root[28 + em] = gr - (b0 + b1);
   }
   __syncwarp();
-  // ---- 7 x 7 Cholesky + solve, every lane redundantly (uniform straight-line code on broadcast loads)
+  // ---- 7 x 7 Cholesky + solve, every lane redundantly (uniform straight-line code on broadcast loads). The indices are
+  // compile-time constants (static_for), so the 28 factor entries stay in registers: with `#pragma unroll` loops the
+  // array went to local memory (ncu r2: 4.9 % of all stall samples at N = 8 on its LDL / STL).
   {
     T Sm[28];
 #pragma unroll
     for (int i = 0; i < 28; i++) Sm[i] = sc.root[i];
 #pragma unroll
     for (int m = 0; m < 7; m++) xr[m] = sc.root[28 + m];
-#pragma unroll
-    for (int j = 0; j < 7; j++) {
-      T d = Sm[j * (j + 1) / 2 + j];
-#pragma unroll
-      for (int k = 0; k < j; k++) d -= Sm[j * (j + 1) / 2 + k] * Sm[j * (j + 1) / 2 + k];
+    static_for<0, 7>([&](auto jc) {
+      constexpr int j = decltype(jc)::value, jj = j * (j + 1) / 2;
+      T d = Sm[jj + j];
+      static_for<0, j>([&](auto kc) { constexpr int k = decltype(kc)::value; d -= Sm[jj + k] * Sm[jj + k]; });
       const T inv = rsqrtT<T>(maxT<T>(d, T(1e-30)));
-      Sm[j * (j + 1) / 2 + j] = inv;                       // 1 / L_jj
-#pragma unroll
-      for (int i = j + 1; i < 7; i++) {
-        T v = Sm[i * (i + 1) / 2 + j];
-#pragma unroll
-        for (int k = 0; k < j; k++) v -= Sm[i * (i + 1) / 2 + k] * Sm[j * (j + 1) / 2 + k];
-        Sm[i * (i + 1) / 2 + j] = v * inv;
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < 7; i++) {
-#pragma unroll
-      for (int k = 0; k < i; k++) xr[i] -= Sm[i * (i + 1) / 2 + k] * xr[k];
-      xr[i] *= Sm[i * (i + 1) / 2 + i];
-    }
-#pragma unroll
-    for (int i = 6; i >= 0; i--) {
-#pragma unroll
-      for (int k = i + 1; k < 7; k++) xr[i] -= Sm[k * (k + 1) / 2 + i] * xr[k];
-      xr[i] *= Sm[i * (i + 1) / 2 + i];
-    }
+      Sm[jj + j] = inv;                                    // 1 / L_jj
+      static_for<j + 1, 7>([&](auto ic) {
+        constexpr int i = decltype(ic)::value, ii = i * (i + 1) / 2;
+        T v = Sm[ii + j];
+        static_for<0, j>([&](auto kc) { constexpr int k = decltype(kc)::value; v -= Sm[ii + k] * Sm[jj + k]; });
+        Sm[ii + j] = v * inv;
+      });
+    });
+    static_for<0, 7>([&](auto ic) {
+      constexpr int i = decltype(ic)::value, ii = i * (i + 1) / 2;
+      static_for<0, i>([&](auto kc) { constexpr int k = decltype(kc)::value; xr[i] -= Sm[ii + k] * xr[k]; });
+      xr[i] *= Sm[ii + i];
+    });
+    static_for<0, 7>([&](auto rc) {
+      constexpr int i = 6 - decltype(rc)::value, ii = i * (i + 1) / 2;
+      static_for<i + 1, 7>([&](auto kc) { constexpr int k = decltype(kc)::value; xr[i] -= Sm[k * (k + 1) / 2 + i] * xr[k]; });
+      xr[i] *= Sm[ii + i];
+    });
   }
   // ---- leaves back: x_c = (y_c - Hc_c . x_root) / D_c - sum_{below} L[i][c] x_i
   T x = gl;

@@ -415,21 +415,22 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
     cn.dist = dist; cn.mu = mu; cn.body1 = b1; cn.body2 = b2; cn.cls1 = c1; cn.cls2 = c2;
     cn.force[0] = cn.force[1] = cn.force[2] = 0; cn.row = -1;
   };
-  // (1) object vs ground: every thread counts, thread 0 writes
+  // (1) object vs ground: lane i of every warp forms candidate i (each warp needs the count), warp 0 writes the up to four
+  // deepest penetrating ones, deepest first, ties by candidate index
   int n1 = 0;
   if (has_obj) {
-    V3<T> pts[8]; T dd[8];
-    int n = plane_candidates<T>(so, gz, pts, dd);
-    T mu = maxT<T>(M.ground_friction, ofric);
-    for (int k = 0; k < 4 && k < n; k++) {
-      int best = -1;
-      for (int i = 0; i < n; i++) if (dd[i] < 0 && (best < 0 || dd[i] < dd[best])) best = i;
-      if (best < 0) break;
-      if (n1 < GMJ_MAXCON) {
-        if (tid == 0) { V3<T> pp = pts[best]; pp.z -= T(0.5) * dd[best]; add_contact(pp, mk<T>(0, 0, 1), dd[best], mu, -1, GMJ_CLS_GROUND, TW::OBJ, GMJ_CLS_OBJECT, n1); }
-        n1++;
-      }
-      dd[best] = 1;
+    V3<T> pc; T dc;
+    plane_candidate_lane<T>(so, gz, lane, pc, dc);
+    int rank = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) { const T dj = __shfl_sync(GMJ_FULL, dc, j); rank += (dj < 0 && (dj < dc || (dj == dc && j < lane))) ? 1 : 0; }
+    const bool pen = lane < 8 && dc < 0;
+    n1 = __popc(__ballot_sync(GMJ_FULL, pen));
+    if (n1 > 4) n1 = 4;
+    if (n1 > GMJ_MAXCON) n1 = GMJ_MAXCON;
+    if (w == 0 && pen && rank < n1) {
+      V3<T> pp = pc; pp.z -= T(0.5) * dc;
+      add_contact(pp, mk<T>(0, 0, 1), dc, maxT<T>(M.ground_friction, ofric), -1, GMJ_CLS_GROUND, TW::OBJ, GMJ_CLS_OBJECT, rank);
     }
   }
   // per-thread geoms: primary (segment plate / palm cylinder) and the hook plate on the tip lanes

@@ -100,8 +100,8 @@ CONTRACT = {
         early_qpos_rel=2e-5,          # 6.5e-6
         early_obs=5e-6,               # 1.7e-6
         early_reward=2e-7,            # 6.0e-8
-        early_evval=1.7e-4,           # 5.7e-5
-        median_rel=5.5e-7, p90_rel=1.2e-6, p99_rel=4e-5, p99_obs=1.7e-5)),    # 1.8e-7, 4.1e-7, 1.3e-5, 5.6e-6
+        early_evval=6e-4,             # 5.7e-5 ... 2.4e-4 between builds that differ in FP32 rounding only (forces in N)
+        median_rel=5.5e-7, p90_rel=1.2e-6, p99_rel=4e-5, p99_obs=2.5e-5)),    # 1.8e-7, 4.1e-7, 1.3e-5, 5.6e-6 ... 8.4e-6
 }
 
 

@@ -278,12 +278,14 @@ def run_config(args, N, envs, K, W, workload, rank, world, local, headline):
         return a_work
 
     def bookkeeping():
-        """MjEnv.step's end of episode: done or 250 steps -> reset -> _spawn_object (3 tries + fallback), two launches."""
+        """MjEnv.step's end of episode: done or 250 steps -> reset -> _spawn_object (3 tries + fallback) -> the first
+        observation of the new episode (MjEnv.reset's return value) into the obs rows of those envs: three launches."""
         ep_steps.add_(1)
         m8 = gb.reset_done(gb.done, EPISODE_CAP)
         gb.spawn_with_retry(0.01, float(np.pi / 2), m8)
+        gb.observe_masked(m8)
         ep_steps.mul_(1 - m8.to(torch.int32))
-        launches[0] += 5       # ours: k_step (set_action pass), k_sort_scatter, k_step (combined), k_reset, k_spawn
+        launches[0] += 6       # ours: k_step (set_action pass), k_sort_scatter, k_step (combined), k_reset, k_spawn, k_observe_masked
 
     def env_step(a_dev):
         out = gb.step(pick_actions(a_dev))

@@ -167,6 +167,14 @@ class GripperBatch:
                                  self._stream()))
         return self.obs, self.reward, self.done, self.events
 
+    def observe_masked(self, mask):
+        """First observation of a new episode (MjEnv.reset's return value) for the envs in `mask`, written into the rows
+        of self.obs; the other rows keep the observation of the step."""
+        m = self._mask(mask)
+        check(self.L.gmj_observe_masked(self.h, _ptr(m), _ptr(self.obs), self._stream()))
+        self._keep = (m,)
+        return self.obs
+
     def set_welds(self, mask_on: int):
         check(self.L.gmj_set_welds(self.h, int(mask_on), self._stream()))
 

@@ -312,6 +312,14 @@ __global__ void k_stats(const EnvState<T, QC>* envs, int n_envs, unsigned long l
   atomicAdd(&out[5], (unsigned long long)e.st_overflow); atomicAdd(&out[6], (unsigned long long)e.st_relaxed); atomicAdd(&out[7], (unsigned long long)e.st_capped);
 }
 
+// MjClass::get_observation of the masked envs straight from the resident state (no stepping, no side effects)
+template <typename T, int QC>
+__global__ void k_observe_masked(const EnvState<T, QC>* envs, const DevSettings* Sp, int n_envs, const uint8_t* mask, float* obs) {
+  int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= n_envs || !mask[env]) return;
+  get_observation<T>(envs[env], *Sp, obs + (size_t)env * Sp->n_obs);
+}
+
 // EventTrack of every env (MjType::EventTrack, src/mjclass.h:575-647): row / abs counters and last values
 template <typename T, int QC>
 __global__ void k_event_track(const EnvState<T, QC>* envs, int n_envs, int32_t* row_abs, float* last, float* cum_reward) {
@@ -692,6 +700,16 @@ int gmj_substeps(GmjHandle* h, int n, int sensors, void* stream) {
 int gmj_observe(GmjHandle* h, float* obs_dev, float* reward_dev, uint8_t* done_dev, float* events_dev, void* stream) {
   if (!h) FAIL("null handle");
   return launch_step(h, STEP_OUTPUT, 0, nullptr, nullptr, obs_dev, reward_dev, done_dev, events_dev, stream);
+}
+
+int gmj_observe_masked(GmjHandle* h, const uint8_t* mask_dev, float* obs_dev, void* stream) {
+  if (!h || !mask_dev || !obs_dev) FAIL("bad argument to gmj_observe_masked");
+  if (!h->hs.obs_ok) FAIL("observation unavailable: sensor history deeper than the device ring (GMJ_WIN) or longer than GMJ_MAX_OBS");
+  DeviceGuard dg_(h->device);
+  int tb = 64, nb = (h->n_envs + tb - 1) / tb;
+  GMJ_FOR_STATE(h, k_observe_masked<T, QC><<<nb, tb, 0, (cudaStream_t)stream>>>((const EnvState<T, QC>*)h->envs, h->settings, h->n_envs, mask_dev, obs_dev));
+  CK(cudaGetLastError());
+  return 0;
 }
 
 int gmj_n_obs(GmjHandle* h) { return h ? h->hs.n_obs : -1; }

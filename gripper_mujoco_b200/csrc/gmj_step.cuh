@@ -89,7 +89,10 @@ template <typename T> __device__ __forceinline__ void copy_words(void* dst, cons
 // The kernel is instruction-fetch bound (ncu: stall_no_inst dominates, the step is ~25 k SASS
 // instructions of mostly straight-line code against a 32 KB L1.5 I-cache), so the warps of a block
 // are kept in lockstep with a block barrier per substep: one fetch stream then feeds WPB warps.
-template <typename T, int N> struct StepCfg { static constexpr int WPB = sizeof(T) == 4 ? (N <= 5 ? GMJ_WPB_F32_N5 : GMJ_WPB_F32_N8) : 4; };
+template <typename T, int N> struct StepCfg {
+  static constexpr int WPB = sizeof(T) == 4 ? (N <= 5 ? GMJ_WPB_F32_N5 : GMJ_WPB_F32_N8) : 4;
+  static constexpr bool MODEL_SMEM = sizeof(T) == 4 && N > 5;        // block copy of DevModel in shared memory (k_step)
+};
 
 template <typename T, int N>
 __global__ void __launch_bounds__(32 * StepCfg<T, N>::WPB, GMJ_BLOCKS_PER_SM)
@@ -132,7 +135,18 @@ k_step(EnvState<T>* __restrict__ envs, const DevModel<T>* __restrict__ Mp, const
     env = valid ? perm[env] : 0;
   }
   WarpShared<T, N>& ws = *reinterpret_cast<WarpShared<T, N>*>(smem_raw + (size_t)warp * sizeof(WarpShared<T, N>));
-  const DevModel<T>& M = *Mp; const DevSettings& S = *Sp;
+  // N = 8 only: the model constants (73 per-lane fields + scalars, 9.9 KB in FP32), read by every lane in every substep,
+  // get one copy per block in shared memory behind the per-warp records -- beside 203 KB of shared memory the L1 is
+  // small (ncu r2: long_sb on the M.f[...] loads; 27.15 -> 26.79 ms at 16384 envs). At N = 5 the L1 holds them and the
+  // copy was measured 4 % SLOWER, so it stays in global memory there.
+  const DevModel<T>* Mq = Mp;
+  if constexpr (StepCfg<T, N>::MODEL_SMEM) {
+    DevModel<T>* const sM = reinterpret_cast<DevModel<T>*>(smem_raw + (size_t)WPB * sizeof(WarpShared<T, N>));
+    for (int i = threadIdx.x; i < (int)(sizeof(DevModel<T>) / 4); i += blockDim.x)
+      reinterpret_cast<unsigned*>(sM)[i] = reinterpret_cast<const unsigned*>(Mp)[i];
+    Mq = sM;
+  }
+  const DevModel<T>& M = *Mq; const DevSettings& S = *Sp;
   if (threadIdx.x == 0) s_nsub_max = 0;
   if (valid) {
     copy_words<T>(&ws.e, &envs[env], sizeof(EnvState<T>), lane);
@@ -223,7 +237,7 @@ int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, co
                           float* reward, uint8_t* done, float* events, cudaStream_t st) {
   const bool combined = (flags & STEP_COMBINED) != 0;
   constexpr int WPB = StepCfg<T, N>::WPB;
-  size_t smem = sizeof(WarpShared<T, N>) * WPB;
+  size_t smem = sizeof(WarpShared<T, N>) * WPB + (StepCfg<T, N>::MODEL_SMEM ? sizeof(DevModel<T>) : 0);   // + the block's copy of the model
   // the opt-in to > 48 KB of dynamic shared memory is PER DEVICE: one flag per device (a handle on a second GPU of
   // the same process would otherwise launch without it and fail)
   static std::atomic<bool> attr_set[GMJ_MAX_DEVICES];

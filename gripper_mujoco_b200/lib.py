@@ -31,7 +31,7 @@ GP = {n: i for i, n in enumerate(PROBE_FIELDS)}
 
 # every symbol include/gmj.h declares (tests check the .so exports exactly these)
 SYMBOLS = ["gmj_create", "gmj_destroy", "gmj_set_settings", "gmj_set_objects", "gmj_reset", "gmj_reset_done", "gmj_spawn",
-           "gmj_step", "gmj_set_action", "gmj_action_step", "gmj_substeps", "gmj_observe", "gmj_n_obs",
+           "gmj_step", "gmj_set_action", "gmj_action_step", "gmj_substeps", "gmj_observe", "gmj_observe_masked", "gmj_n_obs",
            "gmj_n_actions", "gmj_n_envs", "gmj_get_state_host", "gmj_probe_host", "gmj_probe_host_noalloc", "gmj_event_track_host", "gmj_stats",
            "gmj_set_welds", "gmj_last_error"]
 
@@ -132,6 +132,7 @@ def lib():
     L.gmj_action_step.argtypes = [vp, vp]
     L.gmj_substeps.argtypes = [vp, i32, i32, vp]
     L.gmj_observe.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.gmj_observe_masked.argtypes = [vp, vp, vp, vp]
     for f in ("gmj_n_obs", "gmj_n_actions", "gmj_n_envs"):
         getattr(L, f).argtypes = [vp]
     L.gmj_get_state_host.argtypes = [vp, vp, vp]

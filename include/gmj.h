@@ -81,6 +81,11 @@ int gmj_substeps(GmjHandle* h, int n, int sensors, void* stream);
 int gmj_observe(GmjHandle* h, float* obs_dev, float* reward_dev, uint8_t* done_dev, float* events_dev,
                 void* stream);
 
+/* MjEnv.reset() ends with `return self._next_observation()` (rl/env/MjEnv.py:2263): the first observation of the new
+ * episode, for the envs in mask_dev only (uint8[n_envs], e.g. the mask gmj_reset_done returned, after gmj_spawn); the
+ * other rows of obs_dev are left as they are. No side effects on the env state. */
+int gmj_observe_masked(GmjHandle* h, const uint8_t* mask_dev, float* obs_dev, void* stream);
+
 int gmj_n_obs(GmjHandle* h);
 int gmj_n_actions(GmjHandle* h);
 int gmj_n_envs(GmjHandle* h);

@@ -164,6 +164,32 @@ def test_masked_reset_and_determinism():
     gb.close(); g2.close()
 
 
+def test_observe_masked_is_the_first_observation_of_the_new_episode():
+    """gmj_observe_masked (MjEnv.reset's `return self._next_observation()`): rows of the masked envs equal what
+    gmj_observe gives for them, the other rows keep the observation of the step, and the state is not touched."""
+    import torch
+    n = 12
+    mdl, st = make_pair(5, 4e-3, noise=True)
+    gb = _batch(n, mdl, st, "fp32")
+    gb.reset(); gb.spawn_with_retry(0.01, 1.5)
+    rng = np.random.default_rng(1)
+    for _ in range(3):
+        gb.step(rng.integers(0, gb.n_actions - 1, n).astype(np.int32))
+    step_obs = gb.obs.clone()
+    mask = torch.zeros(n, dtype=torch.uint8, device=gb.device); mask[[1, 4, 5, 10]] = 1
+    m = gb.reset_done(mask, 250)
+    assert torch.equal(m, mask)
+    gb.spawn_with_retry(0.01, 1.5, m)
+    q0 = gb.state()[0].copy()
+    got = gb.observe_masked(m).clone()
+    full = gb.observe(obs=True, reward=False, done=False, events=False)[0].clone()
+    mb = mask.bool()
+    assert torch.equal(got[mb], full[mb]) and torch.equal(got[~mb], step_obs[~mb])
+    assert not torch.equal(got[mb], step_obs[mb])
+    assert np.array_equal(q0, gb.state()[0])
+    gb.close()
+
+
 def test_bad_action_is_reported():
     from gripper_mujoco_b200.lib import GmjError
     mdl, st = make_pair(5, 2e-3)

@@ -196,6 +196,8 @@ template <int N> __device__ __forceinline__ bool holds_slot(const TopoW<N>& tp, 
 // slot of weld id's joint (0-2 prismatic, 3-5 revolute, 6 palm)
 __device__ __forceinline__ int weld_slot_w(int id) { return id < 3 ? 32 * id : (id < 6 ? 32 * (id - 3) + 1 : 30); }
 
+#include "gmj_primal_wide.cuh"
+
 template <typename T, int N>
 __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ_WNT>& M, const DevSettings& S, int tid, double dtd, T tip_force) {
   using TW = TopoW<N>;
@@ -648,6 +650,25 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
   env_sync<T, N>(ws);
 
   wide_phase<T, N>();
+#ifndef GMJ_DUAL_WIDE
+  // ------------------------------------------------------------------ primal active-set solve (gmj_primal_wide.cuh)
+  int iters = 0;
+  T g = 0, go = 0;
+  {
+    const T tc = maxT<T>(M.solref_tc, 2 * dt), dr = M.solref_dr, dmax = M.solimp[1];
+    const T kk = rcpT<T>(dmax * dmax * tc * tc * dr * dr), bb = T(2) * rcpT<T>(dmax * tc);
+    T pf = 0;
+    if (nr > 0) iters = primal_solve_w<T, N>(ws, tp, M.solimp, kk, bb, nr, tid, e.nrow_prev == nr, e.fprev, pf, g, go);
+    env_sync<T, N>(ws);
+    if (tid < nr) e.fprev[tid] = pf;
+    if (tid == 0) { e.nrow_prev = nr; ws.ax.niter = iters; }
+  }
+  env_sync<T, N>(ws);
+
+  wide_phase<T, N>();
+  // ------------------------------------------------------------------ constraint force, integration
+  // g = whitened constraint force = x - x_s straight from the primal solution
+#else
   // ------------------------------------------------------------------ A = W W^T, all 96 threads share the entries
   form_A<T, N, GMJ_WNT>(ws, nr, tid, nullptr);
   env_sync<T, N>(ws);
@@ -709,6 +730,7 @@ __device__ void physics_substep_wide(WideShared<T, N>& ws, const DevModel<T, GMJ
     if (tp.act) g += ws.W[r][tp.col] * fr;
     if (tid < 6) go += ws.W[r][B + tid] * fr;
   }
+#endif
   // tau_c = L D^1/2 g
   T tauc;
   {

@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GMJ_LIB: development override to A/B-test differently compiled builds of the same sources
 SO_PATH = os.environ.get("GMJ_LIB") or os.path.join(_HERE, "libgripper_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["gmj_api.cu", "gmj_inst.cu", "gmj_step.cuh", "gmj_wide.cuh", "gmj_physics.cuh", "gmj_primal.cuh", "gmj_tail.cuh", "gmj_collide.cuh",
+SOURCES = ["gmj_api.cu", "gmj_inst.cu", "gmj_step.cuh", "gmj_wide.cuh", "gmj_physics.cuh", "gmj_primal.cuh", "gmj_primal_wide.cuh", "gmj_tail.cuh", "gmj_collide.cuh",
            "gmj_device.cuh"]
 HEADERS = [os.path.join(_HERE, "..", "include", h) for h in ("gmj.h", "gmj_types.h")]
 

@@ -379,6 +379,18 @@ static int build_model(const GmjModel* m, DevModel<T, LN>* d) {
     if (m->parent[i] != exp_parent) FAIL("model tree does not match the lane layout");
     int exp_hinge = (i != 0 && i != B - 1 && ((i - 1) % NL) > 0);
     if (m->jtype[i] != exp_hinge) FAIL("model joint types do not match the lane layout");
+    // the lane-per-dof kernel walks the segments after the first as a planar chain (gmj_physics.cuh, kinematics): their
+    // joints must be hinges about the local y axis, offset along local x, with no fixed rotation between segments
+    if (!wide && i != 0 && i != B - 1 && ((i - 1) % NL) >= 2) {
+      const bool first = ((i - 1) % NL) == 2;
+      const bool ax_ok = fabs(m->axis[i][0]) < 1e-12 && fabs(m->axis[i][1] - 1.0) < 1e-12 && fabs(m->axis[i][2]) < 1e-12;
+      bool rest_ok = true;
+      if (!first) {
+        rest_ok = fabs(m->pos[i][1]) < 1e-12 && fabs(m->pos[i][2]) < 1e-12;
+        for (int k = 0; k < 9; k++) rest_ok = rest_ok && fabs(R[k] - ((k % 4 == 0) ? 1.0 : 0.0)) < 1e-12;
+      }
+      if (!ax_ok || !rest_ok) FAIL("finger segments are not a planar chain (hinges about local y, offsets along local x, no fixed rotations)");
+    }
     d->qpos0[i] = (T)m->qpos0[i];
     int sl[3]; const int ns = slots(i, sl);
     for (int r = 0; r < ns; r++) {

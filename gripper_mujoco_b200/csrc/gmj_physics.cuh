@@ -475,6 +475,7 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   M3<T> R; V3<T> p = mk<T>(0, 0, 0), aw = mk<T>(0, 0, 1), anchor = mk<T>(0, 0, 0);
 #pragma unroll
   for (int k = 0; k < 9; k++) R.m[k] = (k % 4 == 0) ? T(1) : T(0);
+#ifdef GMJ_GENERIC_FK
 #pragma unroll
   for (int d = 0; d <= NL; d++) {
     M3<T> Rp = shflM(R, tp.parent);
@@ -486,6 +487,56 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
       if (!tp.hinge) { R = R0; p = P0 + aw * q; } else { R = mul(R0, rot_axis(axl, q)); p = P0; }
     }
   }
+#else
+  // Base, slides, finger revolute and FIRST segment by the depth walk (4 levels). The segments after the first hang on
+  // parallel hinges (axis y of the previous segment, offset (L, 0, 0), no fixed rotation: checked on the host,
+  // build_model), so the rest of a finger is a PLANAR chain: frame = Rb Roty(sum of angles), anchors = running sum of
+  // L (cos, 0, -sin) in the frame Rb of the first segment's joint. Two short scans replace N - 1 levels of the walk
+  // (each 12 shuffles + two 3x3 products that only the lanes of that depth needed).
+  M3<T> Rb; V3<T> Pb = mk<T>(0, 0, 0);
+#pragma unroll
+  for (int k = 0; k < 9; k++) Rb.m[k] = 0;
+#pragma unroll
+  for (int d = 0; d <= 3; d++) {
+    M3<T> Rp = shflM(R, tp.parent);
+    V3<T> pp = shfl3(p, tp.parent);
+    if (tp.depth == d) {
+      M3<T> R0; V3<T> P0;
+      if (d == 0) { R0 = Rl; P0 = pl; } else { R0 = mul(Rp, Rl); P0 = pp + mul(Rp, pl); }
+      aw = mul(R0, axl); anchor = P0;
+      if (!tp.hinge) { R = R0; p = P0 + aw * q; } else { R = mul(R0, rot_axis(axl, q)); p = P0; }
+      if (d == 3) { Rb = R0; Pb = P0; }
+    }
+  }
+  {
+    const bool seg = tp.chain && tp.local >= 2, tail = tp.chain && tp.local >= 3;
+    const int s = tp.local - 2;                               // segment index inside the finger (0 = first segment)
+    T th = seg ? q : T(0);                                    // inclusive prefix of the segment angles
+#pragma unroll
+    for (int off = 1; off < N; off <<= 1) { const T t = __shfl_up_sync(GMJ_FULL, th, off); if (seg && s >= off) th += t; }
+    const int src = tp.chain ? tp.fb + 2 : lane;
+    Rb = shflM(Rb, src); Pb = shfl3(Pb, src);
+    T sx, cx; sincosT<T>(th - q, &sx, &cx);                   // frame before this segment's own hinge
+    T ux = tail ? pl.x * cx : T(0), uz = tail ? -pl.x * sx : T(0);
+#pragma unroll
+    for (int off = 1; off < N; off <<= 1) {
+      const T tx = __shfl_up_sync(GMJ_FULL, ux, off), tz = __shfl_up_sync(GMJ_FULL, uz, off);
+      if (seg && s >= off) { ux += tx; uz += tz; }
+    }
+    if (tail) {
+      T si, ci; sincosT<T>(th, &si, &ci);
+      aw = mk<T>(Rb.m[1], Rb.m[4], Rb.m[7]);                  // Rb ey: the same world axis for every hinge of the finger
+      anchor = Pb + mk<T>(Rb.m[0] * ux + Rb.m[2] * uz, Rb.m[3] * ux + Rb.m[5] * uz, Rb.m[6] * ux + Rb.m[8] * uz);
+#pragma unroll
+      for (int r = 0; r < 3; r++) {
+        R.m[3 * r] = Rb.m[3 * r] * ci - Rb.m[3 * r + 2] * si;
+        R.m[3 * r + 1] = Rb.m[3 * r + 1];
+        R.m[3 * r + 2] = Rb.m[3 * r] * si + Rb.m[3 * r + 2] * ci;
+      }
+      p = anchor;
+    }
+  }
+#endif
   // local force frames for the tally (xmat of finger_i and palm)
   if (tp.chain && tp.local == 1) { int f = (lane - 1) / NL;
 #pragma unroll

@@ -293,6 +293,70 @@ __device__ inline void extract_forces(const EnvState<T, QC>& e, const WarpAux<T>
 // Why: the FP64 fits + noise (libm log / cos) cost ~60 k cycles on three lanes; inside the lockstep loop every warp of
 // the block waited for whichever env had a tap that substep (r2 per-env cycle counters: 6.3 k cycles of tail work and
 // ~11 k cycles of waiting per substep).
+// The same fit for the three fingers at once, one lane per ROW of the least-squares system (lane f (N + 1) + i = point i
+// of finger f): the (N + 1) x 4 matrix lives in registers, every sum runs over the lanes of the finger in row order by
+// shuffle, so the arithmetic (operands and order) is exactly read_gauge_q's and the result is bit-identical. The serial
+// version kept X / v / y in local memory (FP64, 3 lanes): ncu r2, 5 % of the stall samples of the step at N = 8.
+// q3: the 3 N segment angles of a tap record. Returns the fit of finger f on every lane of its group (lanes >= 3 (N + 1): 0).
+template <typename T, int N>
+__device__ inline float gauge_fit_warp(const T* q3, double L, int lane) {
+  constexpr int n = N + 1;
+  static_assert(3 * n <= 32, "one lane per row of the three fits");
+  const int f = lane / n, i = lane - f * n, base = f * n;
+  const bool on = f < 3;
+  const T* qf = q3 + (on ? f : 0) * N;
+  // point i (i >= 1) sits at the end of segment i - 1: cumulative angle q_0 + ... + q_{i-1}, summed in order
+  double cum = 0;
+  for (int j = 0; j < N; j++) if (on && j < i) cum += (double)qf[j];
+  const double cs = (on && i >= 1) ? L * nd_cos(cum) : 0.0, sn = (on && i >= 1) ? L * nd_sin(cum) : 0.0;
+  double fx = 0, y = 0;
+  for (int j = 1; j < n; j++) {                       // fx[i] = fx[i - 1] + L cos(cum_i): running sums in index order
+    const double cj = __shfl_sync(GMJ_FULL, cs, on ? base + j : lane), sj = __shfl_sync(GMJ_FULL, sn, on ? base + j : lane);
+    if (j <= i) { fx += cj; y += sj; }
+  }
+  double X[4] = { fx * fx * fx, fx * fx, fx, 1.0 };
+  auto ordered_sum = [&](double term, int k) {        // sum over rows i >= k of the finger, in row order
+    double acc = 0;
+    for (int j = 0; j < n; j++) { const double t = __shfl_sync(GMJ_FULL, term, on ? base + j : lane); if (j >= k) acc += t; }
+    return acc;
+  };
+#pragma unroll
+  for (int k = 0; k < 4; k++) {                       // Householder QR, column k
+    double nrm = sqrt(ordered_sum(X[k] * X[k], k));
+    const double xkk = __shfl_sync(GMJ_FULL, X[k], on ? base + k : lane);
+    const double alpha = xkk > 0 ? -nrm : nrm;
+    double v = (i >= k) ? X[k] : 0.0;
+    if (i == k) v -= alpha;
+    const double vn = ordered_sum(v * v, k);
+    const bool skip = nrm == 0 || vn == 0;            // uniform inside a finger's group
+#pragma unroll
+    for (int c = k; c < 4; c++) {
+      double d = ordered_sum(v * X[c], k);
+      d = 2 * d / vn;
+      if (!skip && i >= k) X[c] -= d * v;
+    }
+    double d = ordered_sum(v * y, k);
+    d = 2 * d / vn;
+    if (!skip && i >= k) y -= d * v;
+  }
+  // back substitution on the 4 x 4 triangle held by rows 0-3
+  double coeff[4];
+#pragma unroll
+  for (int k = 3; k >= 0; k--) {
+    double s = __shfl_sync(GMJ_FULL, y, on ? base + k : lane);
+#pragma unroll
+    for (int c = k + 1; c < 4; c++) s -= __shfl_sync(GMJ_FULL, X[c], on ? base + k : lane) * coeff[c];
+    const double xkk = __shfl_sync(GMJ_FULL, X[k], on ? base + k : lane);
+    coeff[k] = (xkk != 0) ? s / xkk : 0;
+  }
+  float yv = 0.0f;
+  const double xp = 50e-3;
+  yv = (float)(yv + coeff[0] * (xp * xp * xp));
+  yv = (float)(yv + coeff[1] * (xp * xp));
+  yv = (float)(yv + coeff[2] * xp);
+  yv = (float)(yv + coeff[3] * 1.0);
+  return on ? yv * 1000 : 0.0f;
+}
 #define GMJ_MAXTAP 8
 #define GMJ_TAP_HDR 6                 // mask, wrist, palm, axial[3]; then 3 N joint angles
 template <typename T, int N, int QC>
@@ -302,9 +366,17 @@ __device__ inline void process_taps(EnvState<T, QC>& e, const DevSettings& S, co
   for (int r = 0; r < ntap; r++) {
     const T* rec = taps + (size_t)r * STRIDE;
     const int mask = (int)rec[0];
-    float gfit = 0.0f;
-    if ((mask & 1) && lane < 3) gfit = read_gauge_q<T, N>(rec + GMJ_TAP_HDR + lane * N, (double)M.segment_length);
-    const float gfit0 = __shfl_sync(GMJ_FULL, gfit, 0), gfit1 = __shfl_sync(GMJ_FULL, gfit, 1), gfit2 = __shfl_sync(GMJ_FULL, gfit, 2);
+    float gfit0 = 0.0f, gfit1 = 0.0f, gfit2 = 0.0f;
+    if (mask & 1) {                                     // warp-uniform
+      if constexpr (3 * (N + 1) <= 32) {
+        const float gfit = gauge_fit_warp<T, N>(rec + GMJ_TAP_HDR, (double)M.segment_length, lane);
+        gfit0 = __shfl_sync(GMJ_FULL, gfit, 0); gfit1 = __shfl_sync(GMJ_FULL, gfit, N + 1); gfit2 = __shfl_sync(GMJ_FULL, gfit, 2 * (N + 1));
+      } else {
+        float gfit = 0.0f;
+        if (lane < 3) gfit = read_gauge_q<T, N>(rec + GMJ_TAP_HDR + lane * N, (double)M.segment_length);
+        gfit0 = __shfl_sync(GMJ_FULL, gfit, 0); gfit1 = __shfl_sync(GMJ_FULL, gfit, 1); gfit2 = __shfl_sync(GMJ_FULL, gfit, 2);
+      }
+    }
     if (lane != 0) continue;
     if (mask & 1) {
       for (int f = 0; f < 3; f++) {

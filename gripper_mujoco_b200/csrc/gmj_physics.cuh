@@ -29,7 +29,7 @@ struct WarpShared {
 #ifdef GMJ_DUAL
   static constexpr int ASZ = GMJ_RMAX * (GMJ_RMAX + 1) / 2;
 #else
-  static constexpr int ASZ = QC == 40 ? 3 * (N + 2) * (N + 3) + 8 * B + 36 + NW + 3 : GMJ_RMAX * (GMJ_RMAX + 1) / 2;
+  static constexpr int ASZ = QC == 40 ? 3 * (N + 2) * (N + 3) + 8 * B + 36 + NW + 3 + 8 : GMJ_RMAX * (GMJ_RMAX + 1) / 2;
 #endif
   T A[ASZ];
   T u[WS + 1];                      // W^T f scratch of the LCP solver
@@ -932,7 +932,8 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
       T Jo[6];
 #pragma unroll
       for (int i = 0; i < 6; i++) Jo[i] = Joc[0][i] + sg2 * Joc[t][i];
-      put_row<T, N>(ws, tp, rsqo, nr + k, xw[0] + sg2 * xw[t], (b2 == B) ? Jo : nullptr, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr, gripper_part ? -1 : -2);
+      put_row<T, N>(ws, tp, rsqo, nr + k, xw[0] + sg2 * xw[t], (b2 == B) ? Jo : nullptr, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr,
+                    gripper_part ? -(10 + ((b1 >= 0 && b1 < B) ? b1 : b2)) : -2);        // -(10 + gripper body lane) / -2: no gripper part
     }
     nr += 4;
   }

@@ -31,6 +31,7 @@ template <typename T, int N> struct PrimalScratch {
   T hc[B][8];               // per leaf: coupling row scaled by D^-1/2 (7) and y D^-1/2
   T root[36];               // Schur complement: 28 packed entries + 7 right-hand sides
   T x[WarpShared<T, N>::NW + 3];   // solution (whitened acceleration)
+  unsigned tmask[4][2];     // rows (lane, lane + 32) whose gripper part lies in finger 0-2 / on the palm
 };
 
 // H x = g for the current active set. act0/act1: this lane's rows lane, lane + 32 active. Returns x in sc.x and this
@@ -52,29 +53,41 @@ __device__ __forceinline__ void primal_factor_solve(WarpShared<T, N>& ws, Primal
   for (int m = 0; m < 7; m++) Hc[m] = 0;
   T Se = (lane < 28 && em == en) ? T(1) : T(0);
   T gr = (lane < 28 && em == en) ? xs[cm] : T(0);
-  // ---- H and g: one rank-one term per active row
+  // ---- H and g: one rank-one term per active row. A row's gripper part lies in ONE leaf block (a finger or the palm),
+  // so every finger walks its own list of active rows: the trip count is the longest list, not the row count.
+  {
+    const int myg = tp.chain ? (lane - 1) / NL : (lane == Topo<N>::PALM ? 3 : -1);
+    unsigned a0 = myg >= 0 ? (sc.tmask[myg][0] & m0) : 0u, a1 = myg >= 0 ? (sc.tmask[myg][1] & m1) : 0u;
+    int trips = 0;
+#pragma unroll
+    for (int gq = 0; gq < 4; gq++) { const int c = __popc(sc.tmask[gq][0] & m0) + __popc(sc.tmask[gq][1] & m1); trips = c > trips ? c : trips; }
 #pragma unroll 1
-  for (int r = 0; r < nr; r++) {
-    if (!(((r < 32 ? m0 >> r : m1 >> (r - 32))) & 1)) continue;
-    const T* wr = ws.W[r];
-    const T s = ws.rjv[r], sa = s * ws.rpos[r];          // 1 / R_r and aref_r / R_r (primal_prepare)
-    T wroot[7];
-    wroot[0] = wr[0];
+    for (int it = 0; it < trips; it++) {
+      if (a0 | a1) {
+        int r;
+        if (a0) { r = __ffs(a0) - 1; a0 &= a0 - 1; } else { r = 32 + __ffs(a1) - 1; a1 &= a1 - 1; }
+        const T* wr = ws.W[r];
+        const T s = ws.rjv[r], sa = s * ws.rpos[r];      // 1 / R_r and aref_r / R_r (primal_prepare)
+        const T wc = wr[lane];
+        const T swc = s * wc;
 #pragma unroll
-    for (int m = 1; m < 7; m++) wroot[m] = wr[B + m - 1];
-    if (ws.rlane[r] != -2) {                              // the row has a gripper part (anything but object-ground / base-only)
-      const T wc = leaf ? wr[lane] : T(0);
-      const T swc = s * wc;
+        for (int k = 0; k < NL; k++) if (k <= tp.local) Hrow[k] += swc * wr[tp.fb + k];
+        Hc[0] += swc * wr[0];
 #pragma unroll
-      for (int k = 0; k < NL; k++) if (k <= tp.local) Hrow[k] += swc * wr[tp.fb + k];
-#pragma unroll
-      for (int m = 0; m < 7; m++) Hc[m] += swc * wroot[m];
-      gl += sa * wc;
+        for (int m = 1; m < 7; m++) Hc[m] += swc * wr[B + m - 1];
+        gl += sa * wc;
+      }
     }
-    // root block
-    {
-      const T a = em == 0 ? wroot[0] : wr[cm], b = en == 0 ? wroot[0] : wr[cn];
-      if (lane < 28) { Se += s * a * b; if (em == en) gr += sa * a; }
+  }
+  // root block: every active row
+  if (lane < 28) {
+#pragma unroll 1
+    for (int r = 0; r < nr; r++) {
+      if (!(((r < 32 ? m0 >> r : m1 >> (r - 32))) & 1)) continue;
+      const T* wr = ws.W[r];
+      const T s = ws.rjv[r], sa = s * ws.rpos[r];
+      const T a = wr[cm], b = wr[cn];
+      Se += s * a * b; if (em == en) gr += sa * a;
     }
   }
   // ---- leaves: LDL^T inside each finger chain (pivot row by shuffle), couplings and right-hand side ride along
@@ -183,18 +196,23 @@ __device__ __forceinline__ void primal_factor_solve(WarpShared<T, N>& ws, Primal
 // unconstrained residual for the cold start. Leaves aref in ws.rpos and 1 / R in ws.rjv.
 template <typename T, int N>
 __device__ __forceinline__ void primal_prepare(WarpShared<T, N>& ws, const T* solimp, T kk, T bb, int nr, int lane, bool warm,
-                                               const T* fprev, bool (&act)[2], int (&type)[2], T (&Rr)[2], T (&aref)[2]) {
-  constexpr int NW = WarpShared<T, N>::NW;
+                                               const T* fprev, bool (&act)[2], int (&type)[2], T (&Rr)[2], T (&aref)[2], int (&grp)[2]) {
+  constexpr int NW = WarpShared<T, N>::NW, NL = N + 2, PALM = 3 * N + 7;
 #pragma unroll
   for (int slot = 0; slot < 2; slot++) {
     const int r = lane + 32 * slot;
-    act[slot] = false; type[slot] = ROW_EQ; Rr[slot] = 1; aref[slot] = 0;
+    act[slot] = false; type[slot] = ROW_EQ; Rr[slot] = 1; aref[slot] = 0; grp[slot] = -1;
     if (slot == 1 && nr <= 32) break;
     if (r < nr) {
       const T pos = ws.rpos[r];
       const T imp = impedance<T>(solimp, pos);
       const T ar = -bb * ws.rjv[r] - kk * imp * pos;
       const int ty = ws.rtype[r];
+      {                                                   // leaf block the row's gripper part lies in (welds / limits: their
+        const int rl = ws.rlane[r];                       // joint lane; contacts: the gripper body's lane, put_row)
+        const int bl = ty == ROW_CONTACT ? (rl <= -10 ? -(rl + 10) : 0) : rl;
+        if (bl > 0) grp[slot] = bl == PALM ? 3 : (bl - 1) / NL;
+      }
       const T* wr = ws.W[r];
       const T* xs = ws.W[nr];
       T n0 = 0, n1 = 0, j0 = 0, j1 = 0;
@@ -245,7 +263,14 @@ __device__ int primal_solve(WarpShared<T, N>& ws, const Topo<N>& tp, const T* so
   const T eps = sizeof(T) == 8 ? T(1e-12) : T(2e-6);
   const int maxit = 40;
   bool act[2]; int type[2]; T Rr[2], aref[2];
-  primal_prepare<T, N>(ws, solimp, kk, bb, nr, lane, warm, fprev, act, type, Rr, aref);
+  int grp[2];
+  primal_prepare<T, N>(ws, solimp, kk, bb, nr, lane, warm, fprev, act, type, Rr, aref, grp);
+#pragma unroll
+  for (int gq = 0; gq < 4; gq++) {
+    const unsigned t0 = __ballot_sync(GMJ_FULL, grp[0] == gq), t1 = __ballot_sync(GMJ_FULL, grp[1] == gq);
+    if (lane == 0) { sc.tmask[gq][0] = t0; sc.tmask[gq][1] = t1; }
+  }
+  __syncwarp();
   const int r0 = lane, r1 = lane + 32;
   const bool two = nr > 32;
   const T* xs = ws.W[nr];

@@ -191,13 +191,30 @@ __device__ __forceinline__ void primal_factor_solve(WarpShared<T, N>& ws, Primal
   __syncwarp();
 }
 
+// Sparse row products: a whitened row is zero outside the base column, ONE leaf block (finger g: columns 1 + g NL ..,
+// palm: column 3 N + 7; g = -1: none) and the six object columns. u.v or |u|^2 over exactly those columns.
+template <typename T, int N, class F>
+__device__ __forceinline__ T row_reduce(int g, F&& term) {
+  constexpr int NL = N + 2, B = 3 * N + 8, PALM = 3 * N + 7;
+  T a0 = term(0), a1 = 0;
+#pragma unroll
+  for (int k = 0; k < 6; k += 2) { a0 += term(B + k); a1 += term(B + k + 1); }
+  if (g >= 0 && g < 3) {
+    const int st = 1 + g * NL;
+#pragma unroll
+    for (int k = 0; k + 1 < NL; k += 2) { a0 += term(st + k); a1 += term(st + k + 1); }
+    if (NL & 1) a0 += term(st + NL - 1);
+  } else if (g == 3) a1 += term(PALM);
+  return a0 + a1;
+}
+
 // Per row (lane = row, rows lane and lane + 32): reference acceleration, regulariser from the row norms
 // (A_rr = |w_r|^2; contacts use the norm of the whitened NORMAL row, the mean of their first two pyramid rows),
 // unconstrained residual for the cold start. Leaves aref in ws.rpos and 1 / R in ws.rjv.
 template <typename T, int N>
 __device__ __forceinline__ void primal_prepare(WarpShared<T, N>& ws, const T* solimp, T kk, T bb, int nr, int lane, bool warm,
                                                const T* fprev, bool (&act)[2], int (&type)[2], T (&Rr)[2], T (&aref)[2], int (&grp)[2]) {
-  constexpr int NW = WarpShared<T, N>::NW, NL = N + 2, PALM = 3 * N + 7;
+  constexpr int NL = N + 2, PALM = 3 * N + 7;
 #pragma unroll
   for (int slot = 0; slot < 2; slot++) {
     const int r = lane + 32 * slot;
@@ -215,32 +232,20 @@ __device__ __forceinline__ void primal_prepare(WarpShared<T, N>& ws, const T* so
       }
       const T* wr = ws.W[r];
       const T* xs = ws.W[nr];
-      T n0 = 0, n1 = 0, j0 = 0, j1 = 0;
+      const int g = grp[slot];
+      const T jx = warm ? T(0) : row_reduce<T, N>(g, [&](int c) { return wr[c] * xs[c]; });
       if (ty == ROW_CONTACT) {
         const int rf = ws.rfirst[r];
         const T* wa = ws.W[rf]; const T* wb = ws.W[rf + 1];
-#pragma unroll
-        for (int c = 0; c + 1 < NW; c += 2) {
-          const T u0 = wa[c] + wb[c], u1 = wa[c + 1] + wb[c + 1];
-          n0 += u0 * u0; n1 += u1 * u1;
-          if (!warm) { j0 += wr[c] * xs[c]; j1 += wr[c + 1] * xs[c + 1]; }
-        }
-        if (NW & 1) { const T u0 = wa[NW - 1] + wb[NW - 1]; n0 += u0 * u0; if (!warm) j0 += wr[NW - 1] * xs[NW - 1]; }
         const T mu = ws.rmu[r];
-        const T Ann = T(0.25) * (n0 + n1);
+        const T Ann = T(0.25) * row_reduce<T, N>(g, [&](int c) { const T u = wa[c] + wb[c]; return u * u; });
         Rr[slot] = 2 * mu * mu * (1 - imp) * rcpT<T>(imp) * (1 + mu * mu) * Ann;
       } else {
-#pragma unroll
-        for (int c = 0; c + 1 < NW; c += 2) {
-          n0 += wr[c] * wr[c]; n1 += wr[c + 1] * wr[c + 1];
-          if (!warm) { j0 += wr[c] * xs[c]; j1 += wr[c + 1] * xs[c + 1]; }
-        }
-        if (NW & 1) { n0 += wr[NW - 1] * wr[NW - 1]; if (!warm) j0 += wr[NW - 1] * xs[NW - 1]; }
-        Rr[slot] = (1 - imp) * rcpT<T>(imp) * (n0 + n1);
+        Rr[slot] = (1 - imp) * rcpT<T>(imp) * row_reduce<T, N>(g, [&](int c) { return wr[c] * wr[c]; });
       }
       Rr[slot] = maxT<T>(Rr[slot], T(1e-15));
       aref[slot] = ar; type[slot] = ty;
-      act[slot] = ty == ROW_EQ || (warm ? fprev[r] > 0 : (j0 + j1) - ar < 0);
+      act[slot] = ty == ROW_EQ || (warm ? fprev[r] > 0 : jx - ar < 0);
     }
   }
   __syncwarp();
@@ -257,7 +262,7 @@ __device__ __forceinline__ void primal_prepare(WarpShared<T, N>& ws, const T* so
 template <typename T, int N>
 __device__ int primal_solve(WarpShared<T, N>& ws, const Topo<N>& tp, const T* solimp, T kk, T bb, int nr, int lane, bool warm,
                             const T* fprev, T (&f)[2], T& dx, T& dxo) {
-  constexpr int NW = WarpShared<T, N>::NW, B = 3 * N + 8;
+  constexpr int B = 3 * N + 8;
   static_assert(sizeof(PrimalScratch<T, N>) <= sizeof(ws.A), "primal scratch must fit the packed-A storage");
   PrimalScratch<T, N>& sc = *reinterpret_cast<PrimalScratch<T, N>*>(ws.A);
   const T eps = sizeof(T) == 8 ? T(1e-12) : T(2e-6);
@@ -285,22 +290,8 @@ __device__ int primal_solve(WarpShared<T, N>& ws, const Topo<N>& tp, const T* so
     primal_factor_solve<T, N>(ws, sc, tp, nr, lane, m0, m1, xl, xr);
     // ---- residuals jar_r = w_r . x - aref_r; force of an active row -jar / R, slack of an inactive row jar
     T j0 = 0, j1 = 0;
-    if (r0 < nr) {
-      const T* wr = ws.W[r0];
-      T a0 = 0, a1 = 0;
-#pragma unroll
-      for (int c = 0; c + 1 < NW; c += 2) { a0 += wr[c] * sc.x[c]; a1 += wr[c + 1] * sc.x[c + 1]; }
-      if (NW & 1) a0 += wr[NW - 1] * sc.x[NW - 1];
-      j0 = (a0 + a1) - aref[0];
-    }
-    if (two && r1 < nr) {
-      const T* wr = ws.W[r1];
-      T a0 = 0, a1 = 0;
-#pragma unroll
-      for (int c = 0; c + 1 < NW; c += 2) { a0 += wr[c] * sc.x[c]; a1 += wr[c + 1] * sc.x[c + 1]; }
-      if (NW & 1) a0 += wr[NW - 1] * sc.x[NW - 1];
-      j1 = (a0 + a1) - aref[1];
-    }
+    if (r0 < nr) { const T* wr = ws.W[r0]; j0 = row_reduce<T, N>(grp[0], [&](int c) { return wr[c] * sc.x[c]; }) - aref[0]; }
+    if (two && r1 < nr) { const T* wr = ws.W[r1]; j1 = row_reduce<T, N>(grp[1], [&](int c) { return wr[c] * sc.x[c]; }) - aref[1]; }
     f0 = act[0] ? -j0 * rcpT<T>(Rr[0]) : T(0); f1 = act[1] ? -j1 * rcpT<T>(Rr[1]) : T(0);
     const T fscale = warp_max(maxT<T>(absT<T>(f0), absT<T>(f1)));
     T epsr = eps;

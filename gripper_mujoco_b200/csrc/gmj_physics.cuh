@@ -1020,9 +1020,12 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
   // tau_c = L D^1/2 g
   T tauc = ldl_mulL<T, N>(tp, Mrow, lb, tp.act ? g * sqrtT<T>(D) : T(0));
   // limit-row forces acting on the base joint enter the wrist force sensor
-  if (lane == 0) {
-    for (int r = 0; r < nr; r++) if (ws.rtype[r] == ROW_LIMIT && ws.rlane[r] == 0) wrist += ws.rmu[r] * e.fprev[r];
-    ws.ax.wrist_z = wrist;
+  {   // lane = row (at most one of the base joint's two limit rows can be active, so the lane sum has one term)
+    T wl = 0;
+    if (lane < nr && ws.rtype[lane] == ROW_LIMIT && ws.rlane[lane] == 0) wl = ws.rmu[lane] * e.fprev[lane];
+    if (lane + 32 < nr && ws.rtype[lane + 32] == ROW_LIMIT && ws.rlane[lane + 32] == 0) wl += ws.rmu[lane + 32] * e.fprev[lane + 32];
+    wl = warp_sum(wl);
+    if (lane == 0) { wrist += wl; ws.ax.wrist_z = wrist; }
   }
   // contact forces in the contact frame (mj_contactForce, pyramidal condim 3)
   if (lane < ncon) {

@@ -462,7 +462,7 @@ def main():
         # BASELINE.json configs[2] / [3]: 16384 envs per GPU, 8-segment fingers, contact-heavy grasp-and-lift episodes
         # (at --gpus 8 this IS configs[3]: 131072 envs, transitions gathered to rank 0 inside e2e); configs[4]: one point
         # of the 24-segment sweep
-        for N, envs, k, w, wl in ((8, 16384, 8, 3, "contact"), (24, 1024, 3, 3, "random")):
+        for N, envs, k, w, wl in ((8, 16384, 8, 3, "contact"), (24, 4096, 3, 3, "random")):
             r = run_config(args, N, envs, k, w, wl, rank, world, local, headline=False)
             if r is not None:
                 r.pop("settings"); r.pop("clocks")

@@ -147,3 +147,27 @@ def configure_settings(p: GripperParams, s: Settings, flags: AutoFlags, backend,
         flags.simsteps = False
         s.sim_steps_per_action = int(math.ceil(s.time_for_action / s.mujoco_timestep))
     return info
+
+
+def calibrate_native(mdl, s: Settings, device: int = 0, precision: str = "fp32", enable: bool = True):
+    """The same calibration through the C ABI's gmj_calibrate (for hosts without this module; here a cross-check):
+    runs calibrate_reset + the parts the auto_* settings ask for, writes the results into `s`, returns the GmjCalib."""
+    import ctypes as C
+
+    from . import lib as gl
+    L = gl.lib()
+    ms, ss = mdl.to_struct(), s.pack()
+    io = gl.GmjCalib()
+    io.set_timestep = int(bool(s.auto_set_timestep) and enable)
+    io.calibrate_gauges = int(bool(s.auto_calibrate_gauges) and enable)
+    io.set_sim_steps = int(bool(s.auto_sim_steps))
+    gl.check(L.gmj_calibrate(C.byref(ms), C.byref(ss), int(device), 0 if precision == "fp32" else 1, C.byref(io)))
+    s.reset_qpos_base = io.reset_qpos[0]
+    for k in range(7):
+        setattr(s, f"reset_qpos_g{k}", io.reset_qpos[1 + k])
+    s.mujoco_timestep = io.timestep
+    s.sim_steps_per_action = int(io.sim_steps_per_action)
+    s.wrist_sensor_Z.raw_value_offset = io.wrist_raw_value_offset
+    s.bending_gauge.normalise = io.bend_gauge_normalise
+    s.sim_gauge_raw_to_N_factor = io.sim_gauge_raw_to_N_factor
+    return io

@@ -856,6 +856,116 @@ int gmj_stats(GmjHandle* h, GmjStats* out) {
   return 0;
 }
 
+// ---- MjClass::configure_settings' auto-calibration on the host side of the C ABI (same control flow and arithmetic as
+// gripper_mujoco_b200/calibration.py, which drives the oracle as well)
+namespace {
+struct CalibRun { std::vector<double> qpos; bool unstable; double si_wrist, gauge0; };
+// one freshly reset scratch env with `st`, stepped n times through gmj_substeps (MjClass._backend in mjclass.py)
+int calib_run(const GmjModel* model, const GmjSettings* st, int device, int precision, int n_substeps, int sensors, CalibRun* out, int* launches) {
+  GmjHandle* h = nullptr;
+  if (gmj_create(model, st, 1, device, precision, 0xC0FFEEu, &h)) return 1;
+  int rc = gmj_substeps(h, n_substeps, sensors, nullptr);
+  out->qpos.assign((size_t)model->B + 7, 0.0);
+  std::vector<double> probe(GMJ_PROBE_LEN, 0.0);
+  GmjStats sv; memset(&sv, 0, sizeof(sv));
+  if (!rc) rc = gmj_get_state_host(h, out->qpos.data(), nullptr);
+  if (!rc) rc = gmj_probe_host(h, probe.data());
+  if (!rc) rc = gmj_stats(h, &sv) == 1;
+  out->unstable = probe[GP_unstable] > 0 || sv.unstable_resets > 0;
+  out->si_wrist = probe[GP_si_wrist]; out->gauge0 = probe[GP_gauge0];
+  const std::string keep = g_err;
+  gmj_destroy(h);
+  if (rc) g_err = keep;
+  (*launches)++;
+  return rc;
+}
+float calib_yield_load(const GmjModel* m) {          // luke::calc_yield_point_load (src/myfunctions.cpp:3587-3606), float arithmetic
+  const double t = m->finger_thickness, w = m->finger_width;
+  const float inertia = (float)((w * pow(t, 3.0)) / 12.0);
+  const float m_max = (215e6f * inertia) / (float)(0.5 * t);
+  return m_max / (float)m->finger_length;
+}
+}  // namespace
+
+int gmj_calibrate(const GmjModel* model, GmjSettings* s, int device, int precision, GmjCalib* io) {
+  if (!model || !s || !io) FAIL("null argument to gmj_calibrate");
+  const int N = model->N, NL = N + 2, B = model->B;
+  io->launches = 0; io->highest_stable_timestep = 0;
+  CalibRun r;
+  // ---- luke::calibrate_reset (src/myfunctions.cpp:1450-1516): 0.8 s settle from the keyframe with every weld on
+  {
+    GmjSettings st = *s;
+    st.general[GS_mujoco_timestep] = 2e-3; st.general[GS_base_position_noise] = 0.0; st.general[GS_curve_validation] = 0.0;
+    st.general[GS_reset_qpos_base] = 0.0;
+    for (int f = 0; f < 3; f++) { st.general[GS_reset_qpos_g0 + 2 * f] = model->qpos0[1 + f * NL]; st.general[GS_reset_qpos_g1 + 2 * f] = 0.0; }
+    st.general[GS_reset_qpos_g6] = model->qpos0[B - 1];
+    int steps = 400; bool ok = false;
+    for (int attempt = 0; attempt < 5 && !ok; attempt++) {     // halve the timestep until the settle is stable (long fingers)
+      if (calib_run(model, &st, device, precision, steps, 0, &r, &io->launches)) return 1;
+      double mx = 0; bool fin = true;
+      for (int i = 0; i < B; i++) { fin = fin && std::isfinite(r.qpos[i]); mx = fmax(mx, fabs(r.qpos[i])); }
+      for (size_t i = 0; i < r.qpos.size(); i++) fin = fin && std::isfinite(r.qpos[i]);
+      ok = !r.unstable && fin && mx < 10.0;
+      if (!ok) { st.general[GS_mujoco_timestep] *= 0.5; steps *= 2; }
+    }
+    if (!ok) FAIL("calibrate_reset: no stable settle found");
+    s->general[GS_reset_qpos_base] = r.qpos[0];
+    for (int f = 0; f < 3; f++) { s->general[GS_reset_qpos_g0 + 2 * f] = r.qpos[1 + f * NL]; s->general[GS_reset_qpos_g1 + 2 * f] = r.qpos[2 + f * NL]; }
+    s->general[GS_reset_qpos_g6] = r.qpos[B - 1];
+  }
+  // ---- MjClass::find_highest_stable_timestep (src/mjclass.cpp:4745-4850): float arithmetic as in the reference
+  if (io->set_timestep) {
+    const float coarse = 0.5e-3f, fine = 50e-6f, test_time = 1.0f, max_dt = 20e-3f;
+    float nxt = 1.0e-3f; bool coarse_pass = true;
+    GmjSettings st = *s;
+    for (;;) {
+      st.general[GS_mujoco_timestep] = (double)nxt;
+      if (calib_run(model, &st, device, precision, (int)(test_time / nxt) + 1, 1, &r, &io->launches)) return 1;
+      if (r.unstable) { coarse_pass = false; nxt = nxt - fine; }
+      else if (coarse_pass) nxt = nxt + coarse;
+      else break;
+      if (nxt < fine) FAIL("no stable timestep found for the simulation");
+      if (nxt > max_dt) { nxt = max_dt; coarse_pass = false; }
+    }
+    const float factor = nxt <= 3.0e-3f ? 0.8f : (nxt < 5.0e-3f ? 0.75f : 0.65f);
+    float fin = nxt * factor;
+    fin = (float)((double)(int)(fin * 1e6f) * 1e-6);
+    s->general[GS_mujoco_timestep] = (double)fin;
+    io->highest_stable_timestep = (double)nxt;
+  }
+  const float yl = calib_yield_load(model);
+  io->yield_load = (double)yl;
+  // ---- MjClass::calibrate_simulated_sensors (src/mjclass.cpp:4643-4676)
+  if (io->calibrate_gauges) {
+    const double norm = (double)(float)(s->general[GS_saturation_yield_factor] * (double)yl);
+    GmjSettings st = *s;
+    st.sensor[GSEN_wrist_Z][GSF_use_normalisation] = 0; st.sensor[GSEN_wrist_Z][GSF_use_noise] = 0; st.sensor[GSEN_wrist_Z][GSF_raw_value_offset] = 0;
+    if (calib_run(model, &st, device, precision, (int)(0.3f / (float)st.general[GS_mujoco_timestep]), 1, &r, &io->launches)) return 1;
+    s->sensor[GSEN_wrist_Z][GSF_raw_value_offset] = r.si_wrist;
+    st = *s;
+    st.general[GS_curve_validation] = 1.0; st.general[GS_tip_force_applied] = norm;
+    bool ok = false;
+    for (int attempt = 0; attempt < 5 && !ok; attempt++) {     // validate_curve_under_force retries at 0.8 x timestep
+      if (calib_run(model, &st, device, precision, (int)(50.0f / (float)st.general[GS_mujoco_timestep]), 1, &r, &io->launches)) return 1;
+      ok = !r.unstable;
+      if (!ok) { st.general[GS_mujoco_timestep] *= 0.8; s->general[GS_mujoco_timestep] = st.general[GS_mujoco_timestep]; }
+    }
+    if (!ok) FAIL("curve validation unstable");
+    s->sensor[GSEN_bending_gauge][GSF_normalise] = r.gauge0;
+    s->general[GS_curve_validation] = 0.0;
+    s->general[GS_sim_gauge_raw_to_N_factor] = norm / r.gauge0;
+  }
+  if (io->set_sim_steps) s->general[GS_sim_steps_per_action] = ceil(s->general[GS_time_for_action] / s->general[GS_mujoco_timestep]);
+  io->timestep = s->general[GS_mujoco_timestep];
+  io->sim_steps_per_action = (int)s->general[GS_sim_steps_per_action];
+  io->wrist_raw_value_offset = s->sensor[GSEN_wrist_Z][GSF_raw_value_offset];
+  io->bend_gauge_normalise = s->sensor[GSEN_bending_gauge][GSF_normalise];
+  io->sim_gauge_raw_to_N_factor = s->general[GS_sim_gauge_raw_to_N_factor];
+  io->reset_qpos[0] = s->general[GS_reset_qpos_base];
+  for (int k = 0; k < 7; k++) io->reset_qpos[1 + k] = s->general[GS_reset_qpos_g0 + k];
+  return 0;
+}
+
 int gmj_set_welds(GmjHandle* h, int mask_on, void* stream) {
   if (!h) FAIL("null handle");
   DeviceGuard dg_(h->device);

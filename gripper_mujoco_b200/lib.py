@@ -32,8 +32,16 @@ GP = {n: i for i, n in enumerate(PROBE_FIELDS)}
 # every symbol include/gmj.h declares (tests check the .so exports exactly these)
 SYMBOLS = ["gmj_create", "gmj_destroy", "gmj_set_settings", "gmj_set_objects", "gmj_reset", "gmj_reset_done", "gmj_spawn",
            "gmj_step", "gmj_set_action", "gmj_action_step", "gmj_substeps", "gmj_observe", "gmj_observe_masked", "gmj_n_obs",
-           "gmj_n_actions", "gmj_n_envs", "gmj_get_state_host", "gmj_probe_host", "gmj_probe_host_noalloc", "gmj_event_track_host", "gmj_stats",
+           "gmj_n_actions", "gmj_n_envs", "gmj_get_state_host", "gmj_probe_host", "gmj_probe_host_noalloc", "gmj_event_track_host", "gmj_stats", "gmj_calibrate",
            "gmj_set_welds", "gmj_last_error"]
+
+
+class GmjCalib(C.Structure):
+    _fields_ = [("set_timestep", C.c_int32), ("calibrate_gauges", C.c_int32), ("set_sim_steps", C.c_int32),
+                ("sim_steps_per_action", C.c_int32), ("highest_stable_timestep", C.c_double), ("timestep", C.c_double),
+                ("wrist_raw_value_offset", C.c_double), ("bend_gauge_normalise", C.c_double),
+                ("sim_gauge_raw_to_N_factor", C.c_double), ("reset_qpos", C.c_double * 8), ("yield_load", C.c_double),
+                ("launches", C.c_int32), ("pad_", C.c_int32)]
 
 
 class GmjStats(C.Structure):
@@ -140,6 +148,7 @@ def lib():
     L.gmj_probe_host_noalloc.argtypes = [vp, vp]
     L.gmj_event_track_host.argtypes = [vp, vp, vp, vp]
     L.gmj_stats.argtypes = [vp, C.POINTER(GmjStats)]
+    L.gmj_calibrate.argtypes = [vp, vp, C.c_int, C.c_int, C.POINTER(GmjCalib)]
     L.gmj_set_welds.argtypes = [vp, i32, vp]
     _LIB = L
     return L

@@ -114,6 +114,14 @@ int gmj_probe_host_noalloc(GmjHandle* h, double* probe_host);
  * last_host float[n_envs][36], and the cumulative reward -> cum_reward_host float[n_envs]. Host-synchronising. */
 int gmj_event_track_host(GmjHandle* h, int32_t* row_abs_host, float* last_host, float* cum_reward_host);
 int gmj_stats(GmjHandle* h, GmjStats* out);
+/* The auto-calibration MjClass::configure_settings runs on the first reset (src/mjclass.cpp:225-314), for hosts that do
+ * not use the Python facade: luke::calibrate_reset, then -- as io->set_timestep / calibrate_gauges / set_sim_steps ask --
+ * find_highest_stable_timestep, calibrate_simulated_sensors (wrist offset, bending-gauge normalisation under the
+ * saturation tip load) and the sim-steps count. Every probe simulation is ONE scratch env created on `device`, stepped
+ * with gmj_substeps and destroyed; `settings` is updated in place, create the production handle with it afterwards.
+ * Host-synchronising; takes ~0.4 s for 5-segment fingers on a B200. Same arithmetic as gripper_mujoco_b200/calibration.py
+ * (tests/test_gpu_parity.py::test_gmj_calibrate_equals_the_python_calibration). */
+int gmj_calibrate(const GmjModel* model, GmjSettings* settings, int device, int precision, GmjCalib* io);
 /* luke::set_all_constraints / apply_segment_force's weld locking (src/myfunctions.cpp:1157-1170,1642-1727): switch the
  * welds in mask_on (bits 0-2 prismatic, 3-5 revolute, 6 palm) on with their anchors at the current joint values, the
  * others off, in every env. Used by the gauge calibration (tip load with the motor joints locked). */

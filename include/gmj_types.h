@@ -168,6 +168,23 @@ typedef struct GmjStateView {
   int32_t pad_;
 } GmjStateView;
 
+/* MjClass::configure_settings' auto-calibration (src/mjclass.cpp:225-314) as one call: which parts to run (the
+ * reference's auto_* settings) and what came out. The results are also written into the GmjSettings passed along. */
+typedef struct GmjCalib {
+  int32_t set_timestep;        /* in: auto_set_timestep     -> find_highest_stable_timestep (src/mjclass.cpp:4745-4850) */
+  int32_t calibrate_gauges;    /* in: auto_calibrate_gauges -> calibrate_simulated_sensors  (src/mjclass.cpp:4643-4676) */
+  int32_t set_sim_steps;       /* in: auto_sim_steps        -> sim_steps_per_action = ceil(time_for_action / timestep)   */
+  int32_t sim_steps_per_action;      /* out */
+  double highest_stable_timestep;    /* out: before the safety factor (0 when set_timestep was off)                      */
+  double timestep;                   /* out: mujoco_timestep in force afterwards                                         */
+  double wrist_raw_value_offset;     /* out: wrist_sensor_Z.raw_value_offset                                             */
+  double bend_gauge_normalise;       /* out: bending_gauge.normalise (gauge reading under the saturation tip load)       */
+  double sim_gauge_raw_to_N_factor;  /* out */
+  double reset_qpos[8];              /* out: calibrate_reset equilibrium, base + 7 motor joints (src/myfunctions.cpp:1450-1516) */
+  double yield_load;                 /* out: luke::calc_yield_point_load (src/myfunctions.cpp:3587-3606)                 */
+  int32_t launches, pad_;            /* out: scratch simulations run                                                      */
+} GmjCalib;
+
 typedef struct GmjStats {
   int64_t substeps;          /* substeps executed since create                    */
   int64_t unstable_resets;   /* BADQACC-equivalent events (src/myfunctions.cpp:4233) */

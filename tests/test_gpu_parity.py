@@ -190,6 +190,29 @@ def test_observe_masked_is_the_first_observation_of_the_new_episode():
     gb.close()
 
 
+def test_gmj_calibrate_equals_the_python_calibration():
+    """gmj_calibrate (C ABI, for hosts without the Python facade) against calibration.py over the same CUDA path:
+    reset pose, highest stable timestep, timestep, sim steps, wrist offset, gauge normalisation -- identical."""
+    from gripper_mujoco_b200 import calibration
+    from gripper_mujoco_b200.mjclass import MjClass
+    from gripper_mujoco_b200.model import GripperParams
+    from gripper_mujoco_b200.settings import Settings
+    for N in (5, 8):
+        mj = MjClass(1, GripperParams(num_segments=N), settings=Settings(), precision="fp32", calibrate=True)
+        a = mj.set
+        b = Settings()
+        io = calibration.calibrate_native(mj.model, b, 0, "fp32")
+        assert io.launches > 10 and io.highest_stable_timestep == mj.highest_stable_timestep
+        assert b.mujoco_timestep == a.mujoco_timestep and b.sim_steps_per_action == a.sim_steps_per_action
+        for k in ["reset_qpos_base"] + [f"reset_qpos_g{j}" for j in range(7)]:
+            assert getattr(b, k) == getattr(a, k), k
+        assert b.wrist_sensor_Z.raw_value_offset == a.wrist_sensor_Z.raw_value_offset
+        assert b.bending_gauge.normalise == a.bending_gauge.normalise
+        assert b.sim_gauge_raw_to_N_factor == a.sim_gauge_raw_to_N_factor
+        assert abs(io.yield_load - mj.yield_load()) < 1e-12
+        mj.close()
+
+
 def test_bad_action_is_reported():
     from gripper_mujoco_b200.lib import GmjError
     mdl, st = make_pair(5, 2e-3)

@@ -19,6 +19,9 @@
 #ifndef GMJ_LIFT_WPB
 #define GMJ_LIFT_WPB 12
 #endif
+#ifndef GMJ_LIFT_SMALL
+#define GMJ_LIFT_SMALL 8            // lift-block warps when the launch is <= 3 rounds of full blocks (A/B: 6 and 4 slower)
+#endif
 #ifndef GMJ_SORT_DIV
 #define GMJ_SORT_DIV 3
 #endif
@@ -250,7 +253,7 @@ int launch_step_TN(GmjHandle* h, int flags, int nsub, const int32_t* actions, co
   // Few envs (<= 3 rounds of full blocks over the SMs): the step is as long as the chain of 3S substeps of the lifting
   // envs, and a block of 8 warps steps faster than a block of 12 (A/B on B200: +3 % at 4096 envs, -6 % at 16384).
   int LW = GMJ_LIFT_WPB < WPB ? GMJ_LIFT_WPB : WPB;
-  if (h->n_sm > 0 && h->n_envs <= 3 * h->n_sm * WPB && LW > 8) LW = 8;
+  if (h->n_sm > 0 && h->n_envs <= 3 * h->n_sm * WPB && LW > GMJ_LIFT_SMALL) LW = GMJ_LIFT_SMALL;
   if (flags & STEP_LIST) blocks = (h->n_envs + LW - 1) / LW;
   const int list_blocks = combined ? (h->n_envs + LW - 1) / LW : 0;   // worst case every env owes a lift; empty list blocks exit at once
   const int bal_sm = combined ? h->balance_sm : 0;

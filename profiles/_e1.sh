@@ -1,1 +1,2 @@
-N=5 ENVS=4096 TAG=r2_k_step_n5 timeout 900 bash profiles/r2_ncu.sh 2>&1 | tail -1
+for v in s10 s12; do GMJ_LIB=$PWD/build/variants/lib_$v.so python profiles/ab_bench.py 4096 5 40 20 2>&1 | tail -1; done
+python profiles/ab_bench.py 4096 5 40 20 2>&1 | tail -1

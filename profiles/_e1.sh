@@ -1,2 +1,4 @@
-for v in s10 s12; do GMJ_LIB=$PWD/build/variants/lib_$v.so python profiles/ab_bench.py 4096 5 40 20 2>&1 | tail -1; done
-python profiles/ab_bench.py 4096 5 40 20 2>&1 | tail -1
+mkdir -p gpurun_out
+(timeout 1500 python -m pytest tests -m gpu -q > gpurun_out/r2_tests.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r2_tests.log); tail -3 gpurun_out/r2_tests.log | cut -c1-200
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -1
+bash profiles/r2_final_run.sh

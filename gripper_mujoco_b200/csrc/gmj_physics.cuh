@@ -896,25 +896,13 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
     V3<T> cp = mk<T>(cn.pos[0], cn.pos[1], cn.pos[2]);
     T mu = cn.mu;
     int b1 = cn.body1, b2 = cn.body2;
-    T Jc[3], Joc[3][6], jvc[3];
+    T Jc[3], jvc[3];
 #pragma unroll
     for (int ax3 = 0; ax3 < 3; ax3++) {
       V3<T> d = mk<T>(cn.frame[3 * ax3], cn.frame[3 * ax3 + 1], cn.frame[3 * ax3 + 2]);
       T j2 = (b2 < B) ? jac_entry<T, N>(tp, b2, cp, d, aw, anchor) : T(0);
       T j1 = jac_entry<T, N>(tp, b1, cp, d, aw, anchor);
       Jc[ax3] = j2 - j1;
-      // object part (body2 == B): linear dofs world, angular dofs body frame
-#pragma unroll
-      for (int k = 0; k < 6; k++) Joc[ax3][k] = 0;
-      if (b2 == B) {
-        Joc[ax3][0] = d.x; Joc[ax3][1] = d.y; Joc[ax3][2] = d.z;
-        V3<T> r = cp - mk<T>(pov[0], pov[1], pov[2]);
-#pragma unroll
-        for (int k = 0; k < 3; k++) {
-          V3<T> axk = mk<T>(Rov[k], Rov[3 + k], Rov[6 + k]);
-          Joc[ax3][3 + k] = dot(d, cross(axk, r));
-        }
-      }
       jvc[ax3] = Jc[ax3] * qd;
     }
 #pragma unroll
@@ -922,22 +910,45 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
 #pragma unroll
       for (int ax3 = 0; ax3 < 3; ax3++) jvc[ax3] += __shfl_xor_sync(GMJ_FULL, jvc[ax3], o);
     }
+    // object part (body2 == B; linear dofs world, angular dofs body frame), one entry per lane: lane 6 a + c holds the
+    // object Jacobian of frame axis a, coordinate c. (Every lane used to form all 18 entries, the four rows' 24 combinations
+    // and lane 0 stored them: ncu r2, put_row's object stores alone were 2.8 % of the stall samples.)
+    const bool objc = b2 == B;
+    T jo = 0;
+    const int ja = lane / 6, jc = lane - 6 * ja;
+    if (objc && lane < 18) {
+      const V3<T> d = mk<T>(cn.frame[3 * ja], cn.frame[3 * ja + 1], cn.frame[3 * ja + 2]);
+      if (jc < 3) jo = jc == 0 ? d.x : (jc == 1 ? d.y : d.z);
+      else {
+        const int k = jc - 3;
+        const V3<T> r = cp - mk<T>(pov[0], pov[1], pov[2]);
+        const V3<T> axk = mk<T>(Rov[k], Rov[3 + k], Rov[6 + k]);
+        jo = dot(d, cross(axk, r));
+      }
+    }
+    if (objc) {                                           // J_obj . v_obj per frame axis: sum over the six lanes of a group
+      const T pv = lane < 18 ? jo * e.qvel[32 + jc] : T(0);
+      const T t1 = pv + __shfl_down_sync(GMJ_FULL, pv, 1);
+      const T t2 = t1 + __shfl_down_sync(GMJ_FULL, t1, 2);
 #pragma unroll
-    for (int ax3 = 0; ax3 < 3; ax3++)
-      jvc[ax3] += (b2 == B) ? (Joc[ax3][0] * e.qvel[32] + Joc[ax3][1] * e.qvel[33] + Joc[ax3][2] * e.qvel[34] + Joc[ax3][3] * e.qvel[35] + Joc[ax3][4] * e.qvel[36] + Joc[ax3][5] * e.qvel[37]) : T(0);
+      for (int ax3 = 0; ax3 < 3; ax3++) jvc[ax3] += __shfl_sync(GMJ_FULL, t2, 6 * ax3) + __shfl_sync(GMJ_FULL, t1, 6 * ax3 + 4);
+    }
     const bool gripper_part = (b1 >= 0 && b1 < B) || (b2 >= 0 && b2 < B);
     T xw[3] = { Jc[0], Jc[1], Jc[2] };
     if (gripper_part) ldl_fwdK<T, N, 3>(tp, Mrow, lb, xw);      // object-ground contacts have no gripper columns
 #pragma unroll
     for (int ax3 = 0; ax3 < 3; ax3++) xw[ax3] *= rsq;
     if (lane == 0) cn.row = nr;
+    if (objc) {                                           // lane 6 k + c: object column c of pyramid row k = n +- mu t
+      const int kr = ja, tr = 1 + (kr >> 1);
+      const T sgl = (kr & 1) ? -mu : mu;
+      const T jn = __shfl_sync(GMJ_FULL, jo, jc), jt = __shfl_sync(GMJ_FULL, jo, lane < 24 ? 6 * tr + jc : lane);
+      if (lane < 24) ws.W[nr + kr][B + jc] = (jn + sgl * jt) * rsqo[jc];
+    }
 #pragma unroll
     for (int k = 0; k < 4; k++) {
       const int t = 1 + (k >> 1); const T sg2 = (k & 1) ? -mu : mu;
-      T Jo[6];
-#pragma unroll
-      for (int i = 0; i < 6; i++) Jo[i] = Joc[0][i] + sg2 * Joc[t][i];
-      put_row<T, N>(ws, tp, rsqo, nr + k, xw[0] + sg2 * xw[t], (b2 == B) ? Jo : nullptr, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr,
+      put_row<T, N>(ws, tp, rsqo, nr + k, xw[0] + sg2 * xw[t], nullptr, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr,
                     gripper_part ? -(10 + ((b1 >= 0 && b1 < B) ? b1 : b2)) : -2);        // -(10 + gripper body lane) / -2: no gripper part
     }
     nr += 4;

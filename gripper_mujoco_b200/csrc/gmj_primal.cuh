@@ -52,6 +52,7 @@ __device__ __forceinline__ void primal_factor_solve(WarpShared<T, N>& ws, Primal
 #pragma unroll
   for (int m = 0; m < 7; m++) Hc[m] = 0;
   T Se = (lane < 28 && em == en) ? T(1) : T(0);
+  unsigned gact = 0;                                     // leaf blocks (fingers 0-2, palm 3) with at least one active row
   T gr = (lane < 28 && em == en) ? xs[cm] : T(0);
   // ---- H and g: one rank-one term per active row. A row's gripper part lies in ONE leaf block (a finger or the palm),
   // so every finger walks its own list of active rows: the trip count is the longest list, not the row count.
@@ -60,7 +61,10 @@ __device__ __forceinline__ void primal_factor_solve(WarpShared<T, N>& ws, Primal
     unsigned a0 = myg >= 0 ? (sc.tmask[myg][0] & m0) : 0u, a1 = myg >= 0 ? (sc.tmask[myg][1] & m1) : 0u;
     int trips = 0;
 #pragma unroll
-    for (int gq = 0; gq < 4; gq++) { const int c = __popc(sc.tmask[gq][0] & m0) + __popc(sc.tmask[gq][1] & m1); trips = c > trips ? c : trips; }
+    for (int gq = 0; gq < 4; gq++) {
+      const int c = __popc(sc.tmask[gq][0] & m0) + __popc(sc.tmask[gq][1] & m1);
+      trips = c > trips ? c : trips; gact |= (c > 0) << gq;
+    }
 #pragma unroll 1
     for (int it = 0; it < trips; it++) {
       if (a0 | a1) {
@@ -81,9 +85,11 @@ __device__ __forceinline__ void primal_factor_solve(WarpShared<T, N>& ws, Primal
   }
   // root block: every active row
   if (lane < 28) {
+    unsigned a0 = m0, a1 = m1;
 #pragma unroll 1
-    for (int r = 0; r < nr; r++) {
-      if (!(((r < 32 ? m0 >> r : m1 >> (r - 32))) & 1)) continue;
+    while (a0 | a1) {
+      int r;
+      if (a0) { r = __ffs(a0) - 1; a0 &= a0 - 1; } else { r = 32 + __ffs(a1) - 1; a1 &= a1 - 1; }
       const T* wr = ws.W[r];
       const T s = ws.rjv[r], sa = s * ws.rpos[r];
       const T a = wr[cm], b = wr[cn];
@@ -126,13 +132,19 @@ __device__ __forceinline__ void primal_factor_solve(WarpShared<T, N>& ws, Primal
   __syncwarp();
   // ---- Schur complement on the root: S -= sum_leaves u u^T, g_root -= sum_leaves u y'
   if (lane < 28) {
+    // only the leaf blocks with an active row have couplings (the others hold zeros); odd lanes sum into a0 / b0,
+    // even lanes into a1 / b1 whatever is skipped, so the sums do not depend on the skipping
     T a0 = 0, a1 = 0, b0 = 0, b1 = 0;
-#pragma unroll 2
-    for (int c = 1; c + 1 < B; c += 2) {
-      a0 += sc.hc[c][em] * sc.hc[c][en]; a1 += sc.hc[c + 1][em] * sc.hc[c + 1][en];
-      b0 += sc.hc[c][em] * sc.hc[c][7]; b1 += sc.hc[c + 1][em] * sc.hc[c + 1][7];
+#pragma unroll
+    for (int gq = 0; gq < 4; gq++) {
+      if (!((gact >> gq) & 1)) continue;
+#pragma unroll
+      for (int k = 0; k < (gq < 3 ? NL : 1); k++) {
+        const int c = 1 + gq * NL + k;
+        const T pa = sc.hc[c][em] * sc.hc[c][en], pb = sc.hc[c][em] * sc.hc[c][7];
+        if (c & 1) { a0 += pa; b0 += pb; } else { a1 += pa; b1 += pb; }
+      }
     }
-    if (!(B & 1)) { a0 += sc.hc[B - 1][em] * sc.hc[B - 1][en]; b0 += sc.hc[B - 1][em] * sc.hc[B - 1][7]; }
     Se -= a0 + a1;
     sc.root[lane] = Se;
     if (em == en) sc.root[28 + em] = gr - (b0 + b1);

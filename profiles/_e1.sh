@@ -1,4 +1,5 @@
 mkdir -p gpurun_out
-(timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q > gpurun_out/r2_par.log 2>&1; echo "rc=$?" >> gpurun_out/r2_par.log)
-tail -4 gpurun_out/r2_par.log
-SKIP_TESTS=1 VARIANTS="base" bash profiles/r2_ab.sh
+(timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/r2_tests.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r2_tests.log)
+tail -5 gpurun_out/r2_tests.log
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
+bash profiles/r2_final_run.sh

@@ -333,6 +333,14 @@ class MjClass:
         cols.append(un(p[:, GP["read_base_z"]], s.base_z_min, s.base_z_max))
         return self._one(np.stack(cols, axis=1).astype(np.float32))
 
+    def self_overlap(self, depth: float = 0.0):
+        """Not a reference call. Per env, the number of gripper geom pairs (finger <-> finger, hook <-> hook, segment <->
+        palm) that overlap by more than `depth` metres in the current pose: contacts the reference simulates and this
+        path does not (selfcheck.py). Synchronising host read, not for the step loop."""
+        from . import selfcheck
+        q, _ = self.batch.state()
+        return selfcheck.self_overlap(self.model, q, depth)[0]
+
     def get_finger_angle(self):
         return self._one(self.batch.probe_field("tend_th").astype(np.float32))     # target_.end.get_th_rad()
 

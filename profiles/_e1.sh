@@ -1,5 +1,3 @@
 mkdir -p gpurun_out
-(timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/r2_tests.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r2_tests.log)
-tail -5 gpurun_out/r2_tests.log
-python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
-bash profiles/r2_final_run.sh
+(timeout 900 python -m pytest tests/test_gpu_contract.py -m gpu -x -q -s > gpurun_out/r2_contract.log 2>&1; echo "rc=$?" >> gpurun_out/r2_contract.log)
+grep -n "self-overlap\|passed\|failed\|rc=" gpurun_out/r2_contract.log

@@ -152,6 +152,13 @@ def test_contract_trajectories_fp32_vs_oracle(N):
     assert m.pop("free_fraction") > 0.5
     for k, v in m.items():
         assert v <= bar[k], (k, v, bar[k])
+    # the numbers above say nothing about gripper <-> gripper contacts (not simulated): measure how
+    # many of the compared env-steps are in a pose where the reference would have made one
+    from gripper_mujoco_b200 import selfcheck
+    mdl = make_pair(N, TIMING[N][0], steps_per_action=TIMING[N][1], noise=True)[0]
+    over = sum(int((selfcheck.self_overlap(mdl, dev["qpos"][t], depth=1e-4)[0] > 0).sum()) for t in range(0, T, 4))
+    print(f"   gripper self-overlap (M9 state): {over} of {len(range(0, T, 4)) * len(spawned)} sampled env-steps")
+    assert over <= 1e-3 * len(range(0, T, 4)) * len(spawned)
 
 
 def episode_stats(tr, n_act, T):
@@ -213,3 +220,13 @@ def test_statistical_protocol_paired_episodes(N):
         assert disagree <= 0.05, (nm, disagree)
     if every:
         assert firedo[:, lifted].mean() > 0.02 and firedo[:, BINARY_NAMES.index("object_contact")].mean() > 0.1, "protocol needs grasps"
+    if N <= 8:          # how many of these env-steps are in the gripper <-> gripper contact state the path does not simulate (M9)
+        from gripper_mujoco_b200 import selfcheck
+        mdl = make_pair(N, TIMING[N][0], steps_per_action=TIMING[N][1], noise=True)[0]
+        ts = list(range(3, T, 8))
+        over = live = 0
+        for t in ts:                         # only while the episode runs (the device keeps stepping a finished env)
+            run = t < lg
+            over += int(((selfcheck.self_overlap(mdl, dev["qpos"][t], depth=1e-4)[0] > 0) & run).sum()); live += int(run.sum())
+        print(f"   gripper self-overlap (M9 state): {over} of {live} sampled env-steps of running episodes")
+        assert over <= 1e-2 * live              # measured on B200: see DESIGN.md section 8

@@ -461,8 +461,8 @@ def main():
     if not args.no_extras and default_run:
         # BASELINE.json configs[2] / [3]: 16384 envs per GPU, 8-segment fingers, contact-heavy grasp-and-lift episodes
         # (at --gpus 8 this IS configs[3]: 131072 envs, transitions gathered to rank 0 inside e2e); configs[4]: one point
-        # of the 24-segment sweep
-        for N, envs, k, w, wl in ((8, 16384, 8, 3, "contact"), (24, 4096, 3, 3, "random")):
+        # of the 24-segment sweep; the same N = 8 shape under the headline's random-action workload beside it
+        for N, envs, k, w, wl in ((8, 16384, 8, 3, "contact"), (8, 16384, 8, 3, "random"), (24, 4096, 3, 3, "random")):
             r = run_config(args, N, envs, k, w, wl, rank, world, local, headline=False)
             if r is not None:
                 r.pop("settings"); r.pop("clocks")

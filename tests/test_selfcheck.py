@@ -74,3 +74,21 @@ def test_open_gripper_is_clear_and_crossed_fingers_are_found(N):
     assert any(e == 6 and palm in (i, j) for e, i, j in hits)
     # a depth threshold larger than the plates' thickness leaves nothing
     assert sc.self_overlap(mdl, qs, depth=0.06)[0].sum() == 0
+
+
+def test_empty_gripper_tilting_in_runs_the_fingers_through_each_other():
+    """The gap as an executable fact: with no object in the scene nothing stops the fingers (no gripper <-> gripper
+    contacts in this restatement, oracle and kernels alike), and the detector reports the pose. The reference would
+    stop the hooks on each other at about the same step."""
+    from common import OracleBatch, make_pair
+    N = 5
+    mdl, st = make_pair(N, 6.857e-3, steps_per_action=30)
+    ob = OracleBatch(1, mdl, st)
+    first = None
+    for t in range(32):
+        ob.step([2])                                   # action 2: tilt in (header-default action table)
+        if first is None and sc.self_overlap(mdl, ob.qpos(), depth=1e-4)[0][0] > 0:
+            first = t + 1
+    assert first is not None and 22 <= first <= 28, first    # 0.01 rad per action: hooks meet at theta = -0.24 rad from home
+    cnt, hits = sc.self_overlap(mdl, ob.qpos(), depth=1e-4)
+    assert cnt[0] >= 3                                 # the three hook pairs are through each other

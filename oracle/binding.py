@@ -54,6 +54,7 @@ def lib():
         L.or_set_weld.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.or_peek.argtypes = [C.c_void_p, C.c_void_p]
         L.or_set_fast.argtypes = [C.c_void_p, C.c_int]
+        L.or_set_self_collision.argtypes = [C.c_void_p, C.c_int]
         L.or_sample.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.or_sample.restype = C.c_int
         L.or_linear_reward.argtypes = [C.c_float] * 4
@@ -97,6 +98,10 @@ class OracleEnv:
     def set_fast(self, on=True):
         """Timed-baseline solver (oracle.h: fast_solver): active-set pivoting without the Gauss-Seidel pre-sweeps."""
         self.L.or_set_fast(self.h, int(bool(on)))
+
+    def set_self_collision(self, on=True):
+        """Gripper <-> gripper contacts (oracle.h: self_collision). Off by default: the CUDA path has none."""
+        self.L.or_set_self_collision(self.h, int(bool(on)))
 
     def set_settings(self, s):
         self._s = s

@@ -262,6 +262,26 @@ void or_collide(OrEnv* e) {
     if (m->g_type[g] == GMJ_GEOM_BOX)
       plane_shape(e, &sg, fmax(m->ground_friction, m->g_friction[g]), m->g_body[g], m->g_class[g]);
   }
+  if (e->self_collision) {
+    /* gripper <-> gripper (off by default, see oracle.h): every geom pair on different bodies that are not parent and
+     * child, geom1 < geom2 like MuJoCo's pair list, which puts them before the gripper <-> object pairs */
+    Shape sh;
+    for (int g = 0; g < m->ngeom; g++) {
+      geom_shape(e, g, &sg);
+      double rg = shape_bound(&sg);
+      for (int h = g + 1; h < m->ngeom; h++) {
+        int bg = m->g_body[g], bh = m->g_body[h];
+        if (bg == bh || m->parent[bg] == bh || m->parent[bh] == bg) continue;
+        geom_shape(e, h, &sh);
+        double d[3]; sub3(d, sh.pos, sg.pos);
+        double rr = rg + shape_bound(&sh);
+        if (dot3(d, d) > rr * rr) continue;
+        double depth, n[3], pos[3];
+        if (mpr_penetration(&sg, &sh, &depth, n, pos))
+          add_contact(e, pos, n, -depth, fmax(m->g_friction[g], m->g_friction[h]), bg, m->g_class[g], bh, m->g_class[h]);
+      }
+    }
+  }
   if (!e->has_object) return;
   double ro = shape_bound(&so);
   for (int g = 0; g < m->ngeom; g++) {

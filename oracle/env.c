@@ -489,6 +489,7 @@ int or_draw_object(OrEnv* e, int n_objects) {
 }
 
 void or_set_fast(OrEnv* e, int on) { e->fast_solver = on; }
+void or_set_self_collision(OrEnv* e, int on) { e->self_collision = on; }
 
 void or_set_script(OrEnv* e, const double* rows, int nrows) {
   e->script = rows; e->script_rows = nrows; e->script_cursor = 0;

@@ -113,6 +113,11 @@ typedef struct OrEnv {
    * Gauss-Seidel sweeps to 1e-13 the parity oracle runs first (same unique solution; bench.py's CPU arms use it so the
    * baseline is not handicapped by the checker's belt and braces) */
   int fast_solver;
+  /* 1: gripper <-> gripper contacts as well (finger <-> finger, hook <-> hook, segment <-> palm; the reference's single
+   * collision group, src/objecthandler.cpp:135-212, with MuJoCo's same-body and parent-child filters). OFF by default:
+   * the CUDA path does not simulate them, and the oracle is its checker. Used by
+   * profiles/r2_m9_effect.py to measure what the gap is worth in returns and success rates. */
+  int self_collision;
 } OrEnv;
 
 /* ---- gripper motor space (src/gripper.h, src/gripper.cpp) */
@@ -156,6 +161,7 @@ void or_settle(OrEnv* e, int nsteps, double dt);   /* calibrate_reset first call
 float or_read_gauge(const OrEnv* e, int finger);   /* read_armadillo_gauge */
 void or_forward(OrEnv* e);                 /* FK + collision only (mj_forward subset) */
 void or_set_weld(OrEnv* e, int id, int on);
+void or_set_self_collision(OrEnv* e, int on);
 int or_struct_size(void);
 int or_spawn_ok(const OrEnv* e, double x, double y, double rot, const double* bbox3);
 int or_spawn_into_scene(OrEnv* e, const GmjObject* o, double x, double y, double zrot, double xrange, double yrange, double rotrange);

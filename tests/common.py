@@ -135,6 +135,8 @@ def _roll_chunk(args):
     for k, eid in enumerate(env_ids):
         e = OracleEnv(w["ms"], w["ss"])
         e.reset(w["seed"], int(eid), int(episode))
+        if os.environ.get("ORACLE_SELF_COLLISION") == "1":      # profiles/r2_m9_effect.py: what the M9 gap is worth
+            e.set_self_collision(True)
         if search is not None:          # MjEnv's spawn policy with the env's own draws (gmj_spawn with tries / fallback)
             e.L.or_spawn_retry.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int]
             e.L.or_spawn_retry(e.h, C.byref(w["objs"][int(obj_idx[k])].obj), *search)

@@ -92,3 +92,25 @@ def test_empty_gripper_tilting_in_runs_the_fingers_through_each_other():
     assert first is not None and 22 <= first <= 28, first    # 0.01 rad per action: hooks meet at theta = -0.24 rad from home
     cnt, hits = sc.self_overlap(mdl, ob.qpos(), depth=1e-4)
     assert cnt[0] >= 3                                 # the three hook pairs are through each other
+
+
+def test_oracle_self_collision_switch_stops_the_hooks():
+    """oracle.h self_collision (off by default, the kernels have no such contacts): with it the three hooks meet instead
+    of passing, the fingers bend and the tilt lags its command; without it nothing changes from the default."""
+    from common import OracleBatch, make_pair
+    mdl, st = make_pair(5, 6.857e-3, steps_per_action=30)
+    runs = {}
+    for on in (False, True, None):
+        ob = OracleBatch(1, mdl, st)
+        if on is not None:
+            ob.envs[0].set_self_collision(on)
+        for t in range(28):
+            ob.step([2])
+        runs[on] = ob.qpos()[0].copy()
+    assert np.array_equal(runs[False], runs[None])
+    NL = 7
+    th_free, th_hit = runs[False][2::NL][:3], runs[True][2::NL][:3]
+    assert np.all(th_hit > th_free + 5e-3)                    # tilt held back by the contact (commanded: -0.274 rad)
+    bend_free, bend_hit = np.abs(runs[False][3:8]).max(), np.abs(runs[True][3:8]).max()
+    assert bend_hit > 4 * bend_free                            # the strip bends against the other hooks
+    assert sc.self_overlap(mdl, runs[True][None], depth=1e-3)[0][0] == 0 < sc.self_overlap(mdl, runs[False][None], depth=1e-3)[0][0]

@@ -28,6 +28,12 @@ struct WarpShared {
   // primal solve (lane-per-dof kernels): only the PrimalScratch of gmj_primal.cuh lives here
 #ifdef GMJ_DUAL
   static constexpr int ASZ = GMJ_RMAX * (GMJ_RMAX + 1) / 2;
+#elif defined(GMJ_SELF_COLLISION)
+  // + the dense (B + 6)^2 normal matrix of the fallback solve for rows that couple two leaf blocks (gmj_primal.cuh), with
+  // its solution vector behind it; it lies over the primal scratch, which that solve does not use
+  static constexpr int ASZ = QC == 40 ? (NW * (NW + 1) / 2 + NW + 3 > 3 * (N + 2) * (N + 3) + 8 * B + 36 + NW + 3 + 8
+                                          ? NW * (NW + 1) / 2 + NW + 3 : 3 * (N + 2) * (N + 3) + 8 * B + 36 + NW + 3 + 8)
+                                      : GMJ_RMAX * (GMJ_RMAX + 1) / 2;
 #else
   static constexpr int ASZ = QC == 40 ? 3 * (N + 2) * (N + 3) + 8 * B + 36 + NW + 3 + 8 : GMJ_RMAX * (GMJ_RMAX + 1) / 2;
 #endif
@@ -450,6 +456,82 @@ template <int NT> __device__ __forceinline__ void phase_idle() {
 #define GMJ_PHASE(k) phase_barrier<NT>(k)
 #endif
 
+#ifdef GMJ_SELF_COLLISION
+// Gripper <-> gripper contacts (M9; the reference's single collision group, src/objecthandler.cpp:135-212): plates and hooks
+// of DIFFERENT fingers, and every plate / hook against the palm cylinder. Same-finger pairs that MuJoCo's parent-child
+// filter lets through are two or more segments apart and cannot meet within the joint limits: not tested.
+// Every finger tests against the next one (0 -> 1, 1 -> 2, 2 -> 0), so each pair of fingers is walked once; geom1 is the
+// geom of the lower finger like MuJoCo's pair list. Returns the new contact count.
+template <typename T, int N>
+__device__ __noinline__ int self_collide(WarpAux<T>& ax, const Shape<T>& sg, const Shape<T>& sh, T bg, T bh, int gtype, int htype,
+                                         int gcls, T gfric, int lane, int ncon) {
+  constexpr int NL = N + 2, PALM = 3 * N + 7;
+  const Topo<N> tp(lane);
+  auto fetch = [&](const Shape<T>& s, int src) {
+    Shape<T> o; o.type = __shfl_sync(GMJ_FULL, s.type, src); o.round = 0;
+    o.size = shfl3(s.size, src); o.pos = shfl3(s.pos, src);
+#pragma unroll
+    for (int k = 0; k < 9; k++) o.R.m[k] = __shfl_sync(GMJ_FULL, s.R.m[k], src);
+    return o;
+  };
+  // one candidate pair per lane: MPR if the bounding spheres overlap, then the hits are emitted in lane order
+  auto pair = [&](bool on, const Shape<T>& mine, T bmine, const Shape<T>& other, int olane, int ocls, T ofr, bool mine_first) {
+    int hit = 0; T dep = 0; V3<T> nn = mk<T>(0, 0, 1), pp = mk<T>(0, 0, 0);
+    if (on && other.type >= 0) {
+      const V3<T> d = other.pos - mine.pos; const T rr = bmine + shape_bound(other);
+      if (dot(d, d) <= rr * rr) {                                  // coordinates relative to my geom (FP32 resolution)
+        Shape<T> a = mine, b = other; a.pos = mk<T>(0, 0, 0); b.pos = d;
+        hit = mine_first ? mpr_penetration<T>(a, b, &dep, &nn, &pp) : mpr_penetration<T>(b, a, &dep, &nn, &pp);
+      }
+    }
+    unsigned hm = __ballot_sync(GMJ_FULL, hit);
+    while (hm) {
+      const int src = __ffs(hm) - 1; hm &= hm - 1;
+      if (ncon < GMJ_MAXCON) {
+        if (lane == src) {
+          DevContact<T>& cn = ax.con[ncon];
+          const V3<T> pos = pp + mine.pos;
+          cn.pos[0] = pos.x; cn.pos[1] = pos.y; cn.pos[2] = pos.z;
+          make_frame<T>(nn, cn.frame);
+          cn.dist = -dep; cn.mu = maxT<T>(gfric, ofr);
+          cn.body1 = mine_first ? lane : olane; cn.cls1 = mine_first ? gcls : ocls;
+          cn.body2 = mine_first ? olane : lane; cn.cls2 = mine_first ? ocls : gcls;
+          cn.force[0] = cn.force[1] = cn.force[2] = 0; cn.row = -1;
+        }
+        ncon++;
+      }
+    }
+  };
+  const int fi = tp.chain ? (lane - 1) / NL : 0, fnext = (fi + 1) % 3;
+  const bool first = fi < fnext;                                   // my finger holds geom1 of the pair
+  const bool hasg = tp.chain && gtype >= 0, hash = tp.chain && htype >= 0;
+#pragma unroll 1
+  for (int j = 2; j < NL; j++) {                                   // partner: segment j - 1 of the next finger (+ its hook)
+    const int pl = tp.chain ? 1 + fnext * NL + j : lane;
+    {                                                              // bounding spheres first: centres and radii only
+      const V3<T> pg = shfl3(sg.pos, pl), ph = shfl3(sh.pos, pl);
+      const T obg = __shfl_sync(GMJ_FULL, bg, pl), obh = __shfl_sync(GMJ_FULL, bh, pl);
+      const int otg = __shfl_sync(GMJ_FULL, gtype, pl), oth = __shfl_sync(GMJ_FULL, htype, pl);
+      auto near = [&](bool on, V3<T> a, T ra, int ot, V3<T> b, T rb) { const V3<T> d = b - a; const T rr = ra + rb; return on && ot >= 0 && dot(d, d) <= rr * rr; };
+      const bool cand = near(hasg, sg.pos, bg, otg, pg, obg) || near(hasg, sg.pos, bg, oth, ph, obh) ||
+                        near(hash, sh.pos, bh, otg, pg, obg) || near(hash, sh.pos, bh, oth, ph, obh);
+      if (!__any_sync(GMJ_FULL, cand)) continue;
+    }
+    const Shape<T> og = fetch(sg, pl), oh = fetch(sh, pl);
+    const int ocls = __shfl_sync(GMJ_FULL, gcls, pl); const T ofr = __shfl_sync(GMJ_FULL, gfric, pl);
+    pair(hasg, sg, bg, og, pl, ocls, ofr, first); pair(hasg, sg, bg, oh, pl, ocls, ofr, first);
+    pair(hash, sh, bh, og, pl, ocls, ofr, first); pair(hash, sh, bh, oh, pl, ocls, ofr, first);
+  }
+  {                                                                // every finger geom against the palm (geom2: the last geom)
+    const Shape<T> op = fetch(sg, PALM);
+    const int ocls = __shfl_sync(GMJ_FULL, gcls, PALM); const T ofr = __shfl_sync(GMJ_FULL, gfric, PALM);
+    pair(hasg, sg, bg, op, PALM, ocls, ofr, true);
+    pair(hash, sh, bh, op, PALM, ocls, ofr, true);
+  }
+  return ncon;
+}
+#endif
+
 template <typename T, int N, int NT>
 __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, const DevSettings& S, int lane, double dtd, T tip_force) {
   const T dt = (T)dtd;
@@ -779,6 +861,25 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
       }
     }
   }
+#ifdef GMJ_SELF_COLLISION
+  // (2b) gripper <-> gripper (M9): behind an early-out, in its own function so that the substep's registers are not
+  // shaped by it. All geom centres lie in their finger's radial plane (120 deg apart), so with every centre further than
+  // rho0 from the gripper axis (world z through the origin: the base is a z slide) two centres of different fingers are
+  // at least sqrt(3) rho0 apart, and every plate is clear of the palm cylinder (r = 22.5 mm).
+  {
+    const T bg = gtype >= 0 ? shape_bound(sg) : T(0), bh = htype >= 0 ? shape_bound(sh) : T(0);
+    T rho2 = T(1e30);
+    if (tp.chain && gtype >= 0) rho2 = sg.pos.x * sg.pos.x + sg.pos.y * sg.pos.y;
+    if (tp.chain && htype >= 0) rho2 = minT<T>(rho2, sh.pos.x * sh.pos.x + sh.pos.y * sh.pos.y);
+    const T bmax = warp_max(tp.chain ? maxT<T>(bg, bh) : T(0));
+    const T rmin2 = -warp_max(-rho2);
+    const T rho0 = T(2) * bmax / T(1.7) + T(0.0225);
+    if (rmin2 < rho0 * rho0) {
+      Shape<T> cg = sg, ch = sh;
+      ncon = self_collide<T, N>(ws.ax, cg, ch, bg, bh, gtype, htype, gcls, gfric, lane, ncon);
+    }
+  }
+#endif
   // (3) object vs gripper geoms: one MPR query per lane (and a second pass for the hooks)
   if (has_obj) {
     T ro = shape_bound(so);
@@ -949,6 +1050,9 @@ __device__ void physics_substep(WarpShared<T, N>& ws, const DevModel<T>& M, cons
     for (int k = 0; k < 4; k++) {
       const int t = 1 + (k >> 1); const T sg2 = (k & 1) ? -mu : mu;
       put_row<T, N>(ws, tp, rsqo, nr + k, xw[0] + sg2 * xw[t], nullptr, ROW_CONTACT, cn.dist, jvc[0] + sg2 * jvc[t], mu, nr,
+#ifdef GMJ_SELF_COLLISION
+                    (b1 >= 0 && b1 < B && b2 >= 0 && b2 < B) ? -3 :            // -3: two gripper bodies, any column (dense solve)
+#endif
                     gripper_part ? -(10 + ((b1 >= 0 && b1 < B) ? b1 : b2)) : -2);        // -(10 + gripper body lane) / -2: no gripper part
     }
     nr += 4;

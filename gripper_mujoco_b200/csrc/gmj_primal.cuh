@@ -203,6 +203,90 @@ __device__ __forceinline__ void primal_factor_solve(WarpShared<T, N>& ws, Primal
   __syncwarp();
 }
 
+#ifdef GMJ_SELF_COLLISION
+// Fallback for row sets with a contact between two gripper bodies (finger <-> finger, hook <-> hook, segment <-> palm):
+// such a row couples two leaf blocks, H is no longer block-arrow. H = I + sum_active w w^T / R is then formed densely
+// ((B + 6)^2, packed lower triangle over the primal scratch), factored by a left-looking warp Cholesky (lane = row, rows
+// lane and lane + 32) and solved for the one right-hand side. Rare, so runtime loops, no unrolling.
+template <typename T, int N>
+__device__ __noinline__ void primal_dense_solve(WarpShared<T, N>& ws, int nr, int lane, unsigned m0, unsigned m1, T* xv) {
+  constexpr int NW = WarpShared<T, N>::NW;
+  T* H = ws.A;
+  const T* xs = ws.W[nr];
+  constexpr int ne = NW * (NW + 1) / 2;
+#pragma unroll 1
+  for (int e0 = 0; e0 < ne; e0 += 32) {                                  // entries dealt 32 at a time, like form_A
+    const int e = e0 + lane; const bool ok = e < ne; const int ee = ok ? e : 0;
+    int i = (int)((sqrtf(8.0f * (float)ee + 1.0f) - 1.0f) * 0.5f);
+    if ((i + 1) * (i + 2) / 2 <= ee) i++;
+    if (i * (i + 1) / 2 > ee) i--;
+    const int j = ee - i * (i + 1) / 2;
+    T a = i == j ? T(1) : T(0);
+    unsigned a0 = m0, a1 = m1;
+#pragma unroll 1
+    while (a0 | a1) {
+      int r;
+      if (a0) { r = __ffs(a0) - 1; a0 &= a0 - 1; } else { r = 32 + __ffs(a1) - 1; a1 &= a1 - 1; }
+      a += ws.rjv[r] * ws.W[r][i] * ws.W[r][j];
+    }
+    if (ok) H[ee] = a;
+  }
+  T g[2];                                                                // right-hand side, rows lane and lane + 32
+#pragma unroll
+  for (int slot = 0; slot < 2; slot++) {
+    const int c = lane + 32 * slot;
+    T v = c < NW ? xs[c] : T(0);
+    unsigned a0 = m0, a1 = m1;
+#pragma unroll 1
+    while ((a0 | a1) && c < NW) {
+      int r;
+      if (a0) { r = __ffs(a0) - 1; a0 &= a0 - 1; } else { r = 32 + __ffs(a1) - 1; a1 &= a1 - 1; }
+      v += ws.rjv[r] * ws.rpos[r] * ws.W[r][c];
+    }
+    g[slot] = v;
+  }
+  __syncwarp();
+#pragma unroll 1
+  for (int j = 0; j < NW; j++) {                                         // column j of L, and the forward substitution with it
+    T v[2];
+#pragma unroll
+    for (int slot = 0; slot < 2; slot++) {
+      const int i = lane + 32 * slot;
+      v[slot] = 0;
+      if (i >= j && i < NW) {
+        T a = H[TRI(i, j)];
+        for (int k = 0; k < j; k++) a -= H[TRI(i, k)] * H[TRI(j, k)];
+        v[slot] = a;
+      }
+    }
+    const T d = __shfl_sync(GMJ_FULL, j < 32 ? v[0] : v[1], j & 31);
+    const T inv = rsqrtT<T>(maxT<T>(d, T(1e-30)));
+    const T gj = __shfl_sync(GMJ_FULL, j < 32 ? g[0] : g[1], j & 31) * inv;      // y_j
+    __syncwarp();
+#pragma unroll
+    for (int slot = 0; slot < 2; slot++) {
+      const int i = lane + 32 * slot;
+      if (i == j) { H[TRI(j, j)] = inv; g[slot] = gj; }                   // 1 / L_jj on the diagonal
+      else if (i > j && i < NW) { const T l = v[slot] * inv; H[TRI(i, j)] = l; g[slot] -= l * gj; }
+    }
+    __syncwarp();
+  }
+#pragma unroll 1
+  for (int j = NW - 1; j >= 0; j--) {                                    // L^T x = y
+    const T xj = __shfl_sync(GMJ_FULL, j < 32 ? g[0] : g[1], j & 31) * H[TRI(j, j)];
+#pragma unroll
+    for (int slot = 0; slot < 2; slot++) {
+      const int i = lane + 32 * slot;
+      if (i == j) g[slot] = xj;
+      else if (i < j) g[slot] -= H[TRI(j, i)] * xj;
+    }
+  }
+  if (lane < NW) xv[lane] = g[0];
+  if (lane + 32 < NW) xv[lane + 32] = g[1];
+  __syncwarp();
+}
+#endif
+
 // Sparse row products: a whitened row is zero outside the base column, ONE leaf block (finger g: columns 1 + g NL ..,
 // palm: column 3 N + 7; g = -1: none) and the six object columns. u.v or |u|^2 over exactly those columns.
 template <typename T, int N, class F>
@@ -217,6 +301,12 @@ __device__ __forceinline__ T row_reduce(int g, F&& term) {
     for (int k = 0; k + 1 < NL; k += 2) { a0 += term(st + k); a1 += term(st + k + 1); }
     if (NL & 1) a0 += term(st + NL - 1);
   } else if (g == 3) a1 += term(PALM);
+#ifdef GMJ_SELF_COLLISION
+  else if (g == 4) {                         // a row between two gripper bodies: any gripper column
+#pragma unroll 1
+    for (int c = 1; c < B; c++) a1 += term(c);
+  }
+#endif
   return a0 + a1;
 }
 
@@ -241,6 +331,9 @@ __device__ __forceinline__ void primal_prepare(WarpShared<T, N>& ws, const T* so
         const int rl = ws.rlane[r];                       // joint lane; contacts: the gripper body's lane, put_row)
         const int bl = ty == ROW_CONTACT ? (rl <= -10 ? -(rl + 10) : 0) : rl;
         if (bl > 0) grp[slot] = bl == PALM ? 3 : (bl - 1) / NL;
+#ifdef GMJ_SELF_COLLISION
+        if (ty == ROW_CONTACT && rl == -3) grp[slot] = 4;
+#endif
       }
       const T* wr = ws.W[r];
       const T* xs = ws.W[nr];
@@ -295,15 +388,32 @@ __device__ int primal_solve(WarpShared<T, N>& ws, const Topo<N>& tp, const T* so
   const T bscale = warp_max(maxT<T>(r0 < nr ? absT<T>(aref[0]) : T(0), (two && r1 < nr) ? absT<T>(aref[1]) : T(0)));
   int best = 1 << 30, patience = 3, it = 0;
   T xl = 0, xr[7];
+  const T* xv = sc.x;                        // solution vector the residuals read
+#ifdef GMJ_SELF_COLLISION
+  // a row between two gripper bodies anywhere in the set: every round of this solve goes through the dense fallback (its
+  // matrix lies over the primal scratch; the solution vector sits behind it)
+  const bool dense = __any_sync(GMJ_FULL, grp[0] == 4 || grp[1] == 4);
+  T* const xdense = ws.A + WarpShared<T, N>::NW * (WarpShared<T, N>::NW + 1) / 2;
+  if (dense) xv = xdense;
+#endif
   T f0 = 0, f1 = 0;
   for (;; ) {
     it++;
     const unsigned m0 = __ballot_sync(GMJ_FULL, act[0]), m1 = __ballot_sync(GMJ_FULL, act[1]);
+#ifdef GMJ_SELF_COLLISION
+    if (dense) {
+      primal_dense_solve<T, N>(ws, nr, lane, m0, m1, xdense);
+      xl = tp.act ? xv[lane] : T(0);
+      xr[0] = xv[0];
+#pragma unroll
+      for (int k = 0; k < 6; k++) xr[1 + k] = xv[B + k];
+    } else
+#endif
     primal_factor_solve<T, N>(ws, sc, tp, nr, lane, m0, m1, xl, xr);
     // ---- residuals jar_r = w_r . x - aref_r; force of an active row -jar / R, slack of an inactive row jar
     T j0 = 0, j1 = 0;
-    if (r0 < nr) { const T* wr = ws.W[r0]; j0 = row_reduce<T, N>(grp[0], [&](int c) { return wr[c] * sc.x[c]; }) - aref[0]; }
-    if (two && r1 < nr) { const T* wr = ws.W[r1]; j1 = row_reduce<T, N>(grp[1], [&](int c) { return wr[c] * sc.x[c]; }) - aref[1]; }
+    if (r0 < nr) { const T* wr = ws.W[r0]; j0 = row_reduce<T, N>(grp[0], [&](int c) { return wr[c] * xv[c]; }) - aref[0]; }
+    if (two && r1 < nr) { const T* wr = ws.W[r1]; j1 = row_reduce<T, N>(grp[1], [&](int c) { return wr[c] * xv[c]; }) - aref[1]; }
     f0 = act[0] ? -j0 * rcpT<T>(Rr[0]) : T(0); f1 = act[1] ? -j1 * rcpT<T>(Rr[1]) : T(0);
     const T fscale = warp_max(maxT<T>(absT<T>(f0), absT<T>(f1)));
     T epsr = eps;

@@ -11,8 +11,13 @@ from .model import GmjModel, GmjObject
 from .settings import GmjSettings
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
+# The same sources compiled with -DGMJ_SELF_COLLISION: gripper <-> gripper contacts (finger <-> finger, hook <-> hook,
+# segment <-> palm) in the lane-per-dof kernels. Opt-in with GMJ_SELF_COLLISION=1 in the
+# environment: ~10 % slower, and the state it adds is entered in ~0 % of the bench workloads' steps.
+SC_SO_PATH = os.path.join(_HERE, "libgripper_b200_sc.so")
 # GMJ_LIB: development override to A/B-test differently compiled builds of the same sources
-SO_PATH = os.environ.get("GMJ_LIB") or os.path.join(_HERE, "libgripper_b200.so")
+BASE_SO_PATH = os.path.join(_HERE, "libgripper_b200.so")
+SO_PATH = os.environ.get("GMJ_LIB") or (SC_SO_PATH if os.environ.get("GMJ_SELF_COLLISION") == "1" else BASE_SO_PATH)
 CSRC = os.path.join(_HERE, "csrc")
 SOURCES = ["gmj_api.cu", "gmj_inst.cu", "gmj_step.cuh", "gmj_wide.cuh", "gmj_physics.cuh", "gmj_primal.cuh", "gmj_primal_wide.cuh", "gmj_tail.cuh", "gmj_collide.cuh",
            "gmj_device.cuh"]
@@ -57,7 +62,7 @@ INSTANCES = [("float", 5, False), ("float", 8, False), ("double", 5, False), ("d
 OBJ_DIR = os.path.join(_HERE, "..", "build", "obj")
 
 
-def nvcc_commands(out: str = SO_PATH, extra: list[str] | None = None, obj_dir: str = OBJ_DIR):
+def nvcc_commands(out: str = BASE_SO_PATH, extra: list[str] | None = None, obj_dir: str = OBJ_DIR):
     """(compile commands, link command): every command is a plain `nvcc` invocation for sm_100a."""
     extra = list(extra or [])
     objs, cmds = [], []
@@ -72,18 +77,18 @@ def nvcc_commands(out: str = SO_PATH, extra: list[str] | None = None, obj_dir: s
     return cmds, link
 
 
-def stale() -> bool:
-    if not os.path.exists(SO_PATH):
+def stale(path: str = BASE_SO_PATH) -> bool:
+    if not os.path.exists(path):
         return True
-    t = os.path.getmtime(SO_PATH)
+    t = os.path.getmtime(path)
     deps = [os.path.join(CSRC, s) for s in SOURCES] + HEADERS
     return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False, out: str = SO_PATH, extra: list[str] | None = None) -> str:
+def build(force: bool = False, verbose: bool = False, out: str = BASE_SO_PATH, extra: list[str] | None = None) -> str:
     """Compile the CUDA extension for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
-    if force or out != SO_PATH or stale():
-        obj_dir = OBJ_DIR if out == SO_PATH else out + ".obj"
+    if force or out != BASE_SO_PATH or stale():
+        obj_dir = OBJ_DIR if out == BASE_SO_PATH else (OBJ_DIR + "_sc" if out == SC_SO_PATH else out + ".obj")
         os.makedirs(obj_dir, exist_ok=True)
         cmds, link = nvcc_commands(out, (extra or []) + (["-Xptxas", "-v"] if verbose else []), obj_dir)
         procs = [subprocess.Popen(c) for c in cmds]
@@ -92,6 +97,13 @@ def build(force: bool = False, verbose: bool = False, out: str = SO_PATH, extra:
             raise subprocess.CalledProcessError(max(rcs), cmds[rcs.index(max(rcs))])
         subprocess.check_call(link)
     return out
+
+
+def build_self_collision(force: bool = False) -> str:
+    """The -DGMJ_SELF_COLLISION build of the same sources (SC_SO_PATH), loaded instead when GMJ_SELF_COLLISION=1."""
+    if force or stale(SC_SO_PATH):
+        build(force=True, out=SC_SO_PATH, extra=["-DGMJ_SELF_COLLISION"])
+    return SC_SO_PATH
 
 
 FMA_SO = os.path.join(_HERE, "libgmj_fma_peak.so")

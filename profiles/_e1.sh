@@ -1,8 +1,3 @@
 mkdir -p gpurun_out
-timeout 500 python bench.py --no-cpu-baseline > gpurun_out/r2_bench_3extras.json 2> gpurun_out/r2_bench_3extras.err; echo "rc=$?"
-python - <<'PY'
-import json
-d = json.load(open("gpurun_out/r2_bench_3extras.json"))
-print("bench", d["value"], d["e2e"]["value"], d["ms_per_step"])
-for x in d["extra"]["configs"]: print("  extra", x["config"]["segments"], x["config"]["workload"][:40], x["value"], x["e2e"]["value"], x["ms_per_step"], x["roofline"]["frac"])
-PY
+(timeout 600 python -m pytest tests/test_gpu_self_collision.py tests/test_gpu_parity.py -m gpu -q > gpurun_out/r2_sc.log 2>&1; echo "rc=$?" >> gpurun_out/r2_sc.log)
+tail -4 gpurun_out/r2_sc.log

@@ -1,3 +1,7 @@
 mkdir -p gpurun_out
-(timeout 600 python -m pytest tests/test_gpu_self_collision.py tests/test_gpu_parity.py -m gpu -q > gpurun_out/r2_sc.log 2>&1; echo "rc=$?" >> gpurun_out/r2_sc.log)
-tail -4 gpurun_out/r2_sc.log
+R=gpurun_out/r2_ab.log; : > $R
+python profiles/ab_bench.py 4096 5 30 12 2>&1 | tail -1 >> $R
+for v in nocol nodense neither; do
+  GMJ_LIB=$PWD/build/variants/lib_$v.so python profiles/ab_bench.py 4096 5 30 12 2>&1 | tail -1 >> $R
+done
+cat $R
